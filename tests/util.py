@@ -1,0 +1,95 @@
+"""Shared helpers for the test-suite: golden-case loading and oracle drivers."""
+import gzip
+import json
+import os
+
+import numpy as np
+
+from oracle import oracle as O
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN = os.path.join(HERE, "golden")
+
+
+def load_cases():
+    with open(os.path.join(GOLDEN, "adversarial.json")) as fh:
+        return json.load(fh)["cases"]
+
+
+def spans_from_conf(c):
+    """1-based inclusive config positions -> python slices, disabled sub-indexes -> 0:0
+    (src/Quade.py:96-116)."""
+    idx2 = bool(c["index2"])
+    mol1 = bool(c["molecular1"])
+    mol2 = idx2 and bool(c["molecular2"])
+    def sp(on, key):
+        return (c["pos"][key][0] - 1, c["pos"][key][1]) if on else (0, 0)
+    return [sp(True, "index1"), sp(idx2, "index2"), sp(mol1, "molecular1"), sp(mol2, "molecular2")]
+
+
+def sample_keys(case):
+    dual = bool(case["conf"]["index2"])
+    return [(s[1] + s[2]) if dual else s[1] for s in case["samples"]]
+
+
+def oracle_params(case):
+    c = case["conf"]
+    return O.OracleParams(dual=c["index2"], spans=spans_from_conf(c), min_qual=c["minimal_qual"],
+                          sample_keys=sample_keys(case), write_undetermined=c["write_undetermined"],
+                          write_pass=c["write_pass"], write_fail=c["write_fail"])
+
+
+def case_chunks(case):
+    return [[s.encode("latin-1") for s in ch] for ch in case["chunks"]]
+
+
+def expected_files(case):
+    return {k: v.encode("latin-1") for k, v in case["expect"]["files"].items()}
+
+
+def files_from_bins(names, per_bin):
+    """per_bin: list over bins of (R1 bytes, R2 bytes) accumulated over chunks -> {filename: bytes} for the
+    files the reference would have created (a bin file exists iff it received a record, FastqWriter.py:55-57)."""
+    out = {}
+    for n, (a, b) in zip(names, per_bin):
+        if len(a) or len(b):
+            out[n + "_R1.fastq.gz"] = bytes(a)
+            out[n + "_R2.fastq.gz"] = bytes(b)
+    return out
+
+
+def run_oracle_chunks(params, chunks):
+    nb = params.nbins
+    acc = [[bytearray(), bytearray()] for _ in range(nb)]
+    counters = np.zeros(nb, dtype=np.int64)
+    for ch in chunks:
+        r = O.demux_batch(params, ch, last=True)
+        counters += r.counters
+        for b in range(nb):
+            acc[b][0] += r.bin_bytes(0, b)
+            acc[b][1] += r.bin_bytes(1, b)
+    return acc, counters
+
+
+def quade_dataset():
+    """The reference's golden vector: 3 chunks x (R1, R4, R2, R3) in the template's wiring
+    (src/Conf_file.py:46-49), decompressed."""
+    d = os.path.join(GOLDEN, "quade_dataset", "dataset")
+    def rd(n):
+        with gzip.open(os.path.join(d, n), "rb") as fh:
+            return fh.read()
+    chunks = [[rd("C%d_R1.fastq.gz" % i), rd("C%d_R4.fastq.gz" % i), rd("C%d_R2.fastq.gz" % i), rd("C%d_R3.fastq.gz" % i)]
+              for i in (1, 2, 3)]
+    res = os.path.join(GOLDEN, "quade_dataset", "result")
+    exp = {}
+    for f in os.listdir(res):
+        if f.endswith(".fastq.gz"):
+            with gzip.open(os.path.join(res, f), "rb") as fh:
+                exp[f] = fh.read()
+    with open(os.path.join(res, "Quade_report.csv"), newline="") as fh:
+        report = fh.readlines()[1:]
+    case = {"conf": {"minimal_qual": 25, "index2": True, "molecular1": True, "molecular2": True,
+                     "pos": {"index1": [1, 4], "index2": [1, 4], "molecular1": [4, 6], "molecular2": [4, 6]},
+                     "write_pass": True, "write_fail": True, "write_undetermined": True},
+            "samples": [["S1", "ACAG", "ACAG"], ["S2", "CTTG", "CTTG"]]}
+    return case, chunks, exp, report
