@@ -1,0 +1,154 @@
+/*
+ * quade_b200.h -- C-ABI of libquade_b200.so: the B200-native demultiplexing hot path of a-slide/Quade.
+ *
+ * The reference (pure Python 2.7) has no FFI; the boundary replaced here is the body of its hot loop.
+ * Each entry point cites the reference interface it stands in for (paths relative to the reference root):
+ *
+ *   quade_ctx_create        <- Quade.__init__ deriving flags/spans/min_qual          src/Quade.py:96-129
+ *                              + Sample.CLASS_INIT(write_*, min_qual)                 src/Sample.py:48-54
+ *   quade_ctx_set_samples   <- Sample.__init__ filling INDEX_TO_SAMPLE                src/Sample.py:132-153
+ *   quade_submit / collect  <- one slice of the `while True` loop of
+ *                              double_index_parser / simple_index_parser              src/Quade.py:195-254
+ *                              = FastqReader x3/4                                     src/pyFastq/FastqReader.py:25-58
+ *                              + FastqSeq slicing/concat                              src/pyFastq/FastqSeq.py:91-101
+ *                              + Sample.FINDER                                        src/Sample.py:56-91
+ *                              + FastqWriter.__call__ / FastqSeq.fastqstr             src/FastqWriter.py:48-74,
+ *                                                                                     src/pyFastq/FastqSeq.py:68-82
+ *   quade_counters          <- Sample.TOTAL/PASS_QUAL/FAIL_QUAL/UNDETERMINED and
+ *                              per-sample pass_qual/fail_qual                         src/Sample.py:32,144
+ *
+ * Plain C, no exceptions cross the boundary.  Every call returns 0 (QUADE_OK) or a negative quade_err;
+ * quade_last_error() gives a thread-local message.  A ctx is single-owner (one host thread per GPU);
+ * different ctxs are independent.  There is NO CPU fallback: without a CUDA device every compute entry
+ * point fails with QUADE_ERR_CUDA.
+ */
+#ifndef QUADE_B200_H
+#define QUADE_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QUADE_ABI_VERSION 1
+
+/* stream order = the order in which the reference pulls records inside one loop iteration
+ * (src/Quade.py:211-214, :241-243): insert read 1, insert read 2, index read 1[, index read 2] */
+enum { QUADE_R1 = 0, QUADE_R2 = 1, QUADE_I1 = 2, QUADE_I2 = 3 };
+enum { QUADE_SPAN_IDX1 = 0, QUADE_SPAN_IDX2 = 1, QUADE_SPAN_MOL1 = 2, QUADE_SPAN_MOL2 = 3 };
+
+typedef enum {
+    QUADE_OK = 0,
+    QUADE_ERR_BLANK_HEADER = -1, /* a parsed record has no name token: the reference dies with IndexError
+                                    (src/pyFastq/FastqReader.py:42) */
+    QUADE_ERR_NOMEM = -2,
+    QUADE_ERR_BAD_SAMPLE = -3,   /* non-ATCGN / duplicate / empty sample index (src/Sample.py:140-141,171-175) */
+    QUADE_ERR_CUDA = -4,         /* no device, or a CUDA call failed */
+    QUADE_ERR_ARG = -5,
+    QUADE_ERR_CAPACITY = -6,     /* batch exceeds the capacities given at ctx creation (bytes, records, pairs) */
+    QUADE_ERR_UNSUPPORTED = -7,  /* fused sample index longer than 32 bases, suffix wider than 255 bytes */
+    QUADE_ERR_STATE = -8         /* collect without submit, samples not set, ... */
+} quade_err;
+
+/* Values Quade.__init__ derives from the config file (src/Quade.py:96-129). */
+typedef struct {
+    int32_t dual;               /* self.idx2 */
+    int32_t span[4][2];         /* python slices [start,end) of idx1, idx2, mol1, mol2; disabled = 0:0 */
+    int32_t min_qual;           /* [quality] minimal_qual */
+    int32_t write_undetermined; /* [output] flags: counters always count, bins with the flag off get no bytes */
+    int32_t write_pass;
+    int32_t write_fail;
+    int32_t n_samples;
+    /* capacities of one batch (0 = defaults: 256 MiB per stream, max_stream_bytes/64 pairs) */
+    uint64_t max_stream_bytes;
+    uint64_t max_pairs;
+    int32_t n_slots;            /* batches in flight (1..4, 0 = 2): submit N+1 while batch N is collected */
+    int32_t reserved;
+} quade_params;
+
+#define QUADE_BATCH_LAST 1u   /* buffers end at end-of-file: a final line without '\n' still is a line and the
+                                 leftovers are dropped (src/pyFastq/FastqReader.py:37,57-58) */
+#define QUADE_BATCH_DEVICE 2u /* stream[] are DEVICE pointers (16-byte aligned); outputs stay on the device */
+
+typedef struct {
+    const uint8_t *stream[4];
+    uint64_t nbytes[4];
+    uint32_t flags;
+    uint32_t reserved;
+    uint64_t ticket; /* caller's tag, returned by collect */
+} quade_batch;
+
+enum { QUADE_K_FRAME = 0, QUADE_K_VALIDATE, QUADE_K_PAIRING, QUADE_K_CLASSIFY, QUADE_K_BINSCAN, QUADE_K_OFFSETS,
+       QUADE_K_COMPACT, QUADE_K_COUNT };
+
+/* bins: 0 = Undetermined, 1+2s = <sample s>_pass, 2+2s = <sample s>_fail (src/Sample.py:44,147-148) */
+typedef struct {
+    uint64_t ticket;
+    uint64_t n_pairs;          /* Sample.TOTAL increment of this batch */
+    uint64_t consumed[4];      /* bytes of each stream covered by the paired records; the rest is carry-over */
+    uint64_t n_skipped[4];     /* records with len(seq) != len(qual) inside consumed[] (FastqReader.py:48-50) */
+    const uint8_t *out[2];     /* R1 / R2 output arenas, bins concatenated in bin order (pinned host memory, or
+                                  device memory for QUADE_BATCH_DEVICE); valid until the slot is reused */
+    const uint64_t *bin_off[2];/* nbins+1 offsets into out[k] (host memory) */
+    const int64_t *counters;   /* nbins pair counts of this batch (host memory) */
+    int32_t nbins;
+    int32_t err;               /* QUADE_OK or QUADE_ERR_BLANK_HEADER / QUADE_ERR_CAPACITY for this batch */
+    float ms_h2d, ms_kernels, ms_d2h;     /* CUDA-event durations of the three legs */
+    float ms_kernel[QUADE_K_COUNT];       /* per kernel stage, events on the compute stream */
+    uint64_t in_bytes;         /* sum of consumed[] */
+    uint64_t out_bytes;        /* bin_off[0][nbins] + bin_off[1][nbins] */
+    uint64_t gpu_launches;     /* kernels launched for this batch */
+} quade_result;
+
+int quade_version(void);
+const char *quade_last_error(void);
+int quade_device_count(int *count);
+
+/* pinned, caller-visible, library-owned host memory for staging */
+int quade_host_alloc(void **ptr, uint64_t nbytes);
+int quade_host_free(void *ptr);
+
+typedef struct quade_ctx quade_ctx;
+int quade_ctx_create(int device, const quade_params *params, quade_ctx **out);
+int quade_ctx_destroy(quade_ctx *ctx);
+
+/* keys: concatenated fused sample indexes exactly as written in the config (index1_seq + index2_seq);
+ * key_off: n_samples+1 offsets.  Builds the perfect-hash table and uploads it. */
+int quade_ctx_set_samples(quade_ctx *ctx, const uint8_t *keys, const uint32_t *key_off);
+
+/* asynchronous: H2D copy (copy stream) -> kernels (compute stream); returns once everything is enqueued */
+int quade_submit(quade_ctx *ctx, const quade_batch *batch);
+/* blocks until the oldest submitted batch is done, copies its bins back (D2H stream) and describes them */
+int quade_collect(quade_ctx *ctx, quade_result *res);
+
+/* cumulative pair counts since ctx creation / reset: int64[1+2*n_samples] in bin order */
+int quade_counters(quade_ctx *ctx, int64_t *out);
+int quade_counters_reset(quade_ctx *ctx);
+/* CUDA stream handle (cudaStream_t) kernels are launched on, for callers that time with their own events */
+int quade_compute_stream(quade_ctx *ctx, void **stream);
+
+/* --- synthetic dual/single-indexed paired-end data (SURVEY.md section 8(d) generator), host side -------------
+ * Used by bench.py and the tests to make inputs; not part of the demultiplexing path. */
+typedef struct {
+    uint64_t seed;
+    int32_t dual;         /* 0: R1,R2,I1   1: R1,R2,I1,I2 */
+    int32_t read_len;     /* insert read length (150) */
+    int32_t index_len;    /* sample barcode bases per index read */
+    int32_t mol_len;      /* molecular bases following the barcode on each index read */
+    int32_t n_samples;
+    int32_t floor_mode;   /* 0: per-pair phred floor 30 w.p. 0.9 else 2;  1: floor uniform 2..40 */
+    double undetermined;  /* probability that the barcode is random */
+} quade_synth_params;
+
+/* barcodes: n_samples * index_len * (dual?2:1) bytes, pairwise Hamming distance >= 3 per index */
+int quade_synth_barcodes(const quade_synth_params *p, uint8_t *barcodes);
+/* sizes of the 4 streams for pairs [first, first+count) */
+int quade_synth_sizes(const quade_synth_params *p, const uint8_t *barcodes, uint64_t first, uint64_t count,
+                      uint64_t nbytes[4]);
+/* fill the streams (buffers sized by quade_synth_sizes) using n_threads host threads */
+int quade_synth_fill(const quade_synth_params *p, const uint8_t *barcodes, uint64_t first, uint64_t count,
+                     uint8_t *const stream[4], int n_threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

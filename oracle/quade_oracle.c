@@ -70,11 +70,14 @@ static int next_record(cursor *c, record *r, int *valid)
     return 1;
 }
 
-/* generator step: skip invalid records of THIS stream only (FastqReader.py:48-50) */
+/* generator step: skip invalid records of THIS stream only (FastqReader.py:48-50).
+ * returns 1 = valid record, 0 = exhausted, -1 = a parsed record had no name token: the reference raises
+ * IndexError at FastqReader.py:42, i.e. BEFORE the length assertion and whatever the other streams hold. */
 static int next_valid(cursor *c, record *r)
 {
     int valid;
     while (next_record(c, r, &valid)) {
+        if (c->blank_seen) return -1;
         if (valid) return 1;
         c->skipped++;
     }
@@ -202,10 +205,9 @@ int qo_demux_batch(const qo_params *p, const uint8_t *const stream[4], const uin
     for (;;) {                                         /* while True:  Quade.py:210 / :240 */
         record rec[4];
         int got = 1;
-        for (int s = 0; s < ns && got; s++) got = next_valid(&cur[s], &rec[s]);   /* Quade.py:211-214 */
+        for (int s = 0; s < ns && got > 0; s++) got = next_valid(&cur[s], &rec[s]);   /* Quade.py:211-214 */
+        if (got < 0) { err = QO_ERR_BLANK_HEADER; goto done; }
         if (!got) break;                               /* StopIteration: end of chunk, Quade.py:223 */
-        for (int s = 0; s < ns; s++)
-            if (cur[s].blank_seen) { err = QO_ERR_BLANK_HEADER; goto done; }
         for (int s = 0; s < ns; s++) { res->consumed[s] = cur[s].pos; res->n_skipped[s] = cur[s].skipped; }
         res->n_pairs++;                                /* Sample.TOTAL += 1, Sample.py:62 */
 

@@ -1,0 +1,122 @@
+// quade_dev.h -- structures shared by the kernels (quade_kernels.cu) and the C-ABI (quade_api.cu).
+//
+// HBM layout of one batch slot (all offsets are u32: a stream batch is < 3.75 GiB)
+//   per stream s (R1, R2, I1[, I2]):
+//     data[n]                     the raw FASTQ bytes (16-byte aligned base)
+//     nl[4*cap_rec]               position of every '\n' (line k ends at nl[k]); record j = lines 4j..4j+3
+//     e1[cap_rec], e3[cap_rec]    rstripped end of the sequence / quality line of record j
+//     noff[cap_rec], nlen[cap_rec] name token of record j (FastqReader.py:42)
+//     rec[cap_rec] (uint4)        per VALID record, compacted: {name_off, seq_off, qual_off, seq_len}
+//     vnlen[cap_rec], vrec[cap_rec] name_len and record index of the v-th valid record
+//   per pair p:
+//     cls[p]   bin | suffix_len << 16 | written << 31
+//     len1[p], len2[p]            output record bytes (0 when the bin's writer is off)
+//     out1[p], out2[p]            byte offset of the pair's R1 / R2 record inside the output arena
+//     suffix[p * suf_cap]         ':' index [':' molecular] '\n' as raw bytes
+//   per block of pairs_per_block pairs: hist[block][2][nbins] output bytes per bin (R1, R2)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace quade {
+
+constexpr int kMaxStreams = 4;
+constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
+
+// device-resident scalars of one batch; copied back to the host as a whole
+struct BatchState {
+    uint32_t n_lines[kMaxStreams];
+    uint32_t n_valid[kMaxStreams];
+    uint32_t first_blank[kMaxStreams]; // lowest record index with an empty name token, or 0xffffffff
+    uint32_t n_pairs;
+    uint32_t n_blocks;
+    uint32_t consumed[kMaxStreams];
+    uint32_t n_skipped[kMaxStreams];
+    uint32_t err_capacity;             // some array would have overflowed
+    uint32_t err_blank;                // blank header inside the parsed range
+    uint32_t ticket_frame;             // dynamic tile counters
+    uint32_t ticket_validate[kMaxStreams];
+    uint32_t pad;
+    unsigned long long out_total[2];   // bytes of the R1 / R2 arenas
+};
+
+struct StreamDev {
+    const uint8_t *data;
+    uint32_t n;
+    uint32_t cap_rec;
+    uint32_t *nl;
+    uint32_t *e1, *e3, *noff, *nlen;
+    uint4 *rec;
+    uint32_t *vnlen, *vrec;
+    unsigned long long *status_frame;    // decoupled look-back words, one per 16 KiB tile
+    unsigned long long *status_validate; // one per 1024-record tile
+};
+
+struct HashTable {
+    const uint4 *entries;     // {key lo, key hi, nmask, len | (sample+1) << 8}
+    const uint16_t *disp;     // per-bucket displacement
+    uint32_t n_buckets_mask;  // buckets - 1 (power of two)
+    uint32_t n_slots_mask;    // slots - 1 (power of two)
+    uint64_t seed;
+};
+
+struct BatchDev {
+    StreamDev st[kMaxStreams];
+    int n_streams;
+    int dual;
+    int last;
+    int span[4][2];
+    int min_qual;
+    int wr_und, wr_pass, wr_fail;
+    int n_bins;
+    uint32_t cap_pairs;
+    uint32_t pairs_per_block;
+    uint32_t cap_blocks;
+    uint32_t suf_cap;          // bytes per suffix slot (multiple of 4)
+    unsigned long long out_cap[2];
+    BatchState *state;
+    HashTable table;
+    uint32_t *cls, *len1, *len2, *out1, *out2;
+    uint8_t *suffix;
+    uint32_t *hist;            // [cap_blocks][2][n_bins]
+    unsigned long long *bin_total; // [2][n_bins] scratch
+    unsigned long long *bin_off;   // [2][n_bins+1]
+    long long *counters;       // [n_bins] pair counts of this batch
+    uint8_t *out[2];
+    uint32_t frame_tile_start[kMaxStreams + 1];
+};
+
+// hash shared by the host builder and the device probe
+__host__ __device__ inline uint64_t mix64(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__host__ __device__ inline uint64_t key_hash(uint64_t key, uint32_t nmask, uint32_t len, uint64_t seed)
+{
+    return mix64(key ^ mix64(((uint64_t)nmask << 8 | len) ^ seed));
+}
+__host__ __device__ inline uint32_t key_slot(uint64_t h, uint32_t disp, uint32_t slots_mask)
+{
+    uint32_t stride = ((uint32_t)(h >> 12) & slots_mask) | 1u;
+    return ((uint32_t)(h >> 36) + disp * stride) & slots_mask;
+}
+
+// launchers (quade_kernels.cu).  All enqueue on `s`; sizes unknown to the host are read from BatchState.
+void launch_frame(const BatchDev &b, cudaStream_t s);
+void launch_validate(const BatchDev &b, cudaStream_t s);
+void launch_pairing(const BatchDev &b, cudaStream_t s);
+void launch_classify(const BatchDev &b, cudaStream_t s);
+void launch_binscan(const BatchDev &b, cudaStream_t s);
+void launch_offsets(const BatchDev &b, cudaStream_t s);
+void launch_compact(const BatchDev &b, cudaStream_t s);
+int kernel_launch_count(int stage);
+size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
+
+constexpr int kFrameTile = 16384;   // bytes per frame tile
+constexpr int kFrameHalo = 256;
+constexpr int kValidateTile = 1024; // records per validate tile
+
+} // namespace quade

@@ -1,0 +1,140 @@
+"""GPU parity: the CUDA path (through the C-ABI) against the pinned C oracle and the committed golden vectors.
+Bit-exact: byte-identical per-bin streams, identical counters / consumed / skipped."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _ctx_for(case_or_params, **kw):
+    from quade_b200 import DemuxContext
+    p = case_or_params if isinstance(case_or_params, O.OracleParams) else util.oracle_params(case_or_params)
+    return DemuxContext(p.dual, p.spans, p.min_qual, p.sample_keys, p.write_undetermined, p.write_pass, p.write_fail,
+                        **kw), p
+
+
+def _assert_same(res, ref, nbins, tag=""):
+    assert res.n_pairs == ref.n_pairs, tag
+    assert (res.counters == ref.counters).all(), tag
+    assert res.consumed[:len(ref.consumed)] == ref.consumed, tag
+    assert res.n_skipped[:len(ref.n_skipped)] == ref.n_skipped, tag
+    for k in range(2):
+        assert (res.bin_off[k] == ref.bin_off[k]).all(), tag
+        assert res.arena(k).tobytes() == ref.out[k], tag
+
+
+def test_golden_dataset_byte_identical():
+    """The reference's own golden vector (test/dataset -> test/result), incl. the skipped-record desync (299 pairs)."""
+    case, chunks, exp, report = util.quade_dataset()
+    ctx, p = _ctx_for(case, max_stream_bytes=1 << 20, max_pairs=4096)
+    acc = [[bytearray(), bytearray()] for _ in range(p.nbins)]
+    for ch in chunks:
+        r = ctx.run(ch, last=True)
+        for b in range(p.nbins):
+            acc[b][0] += r.bin_bytes(0, b)
+            acc[b][1] += r.bin_bytes(1, b)
+    names = O.bin_names([s[0] for s in case["samples"]])
+    got = util.files_from_bins(names, acc)
+    assert sorted(got) == sorted(exp)
+    for f in exp:
+        assert got[f] == exp[f], f
+    counters = ctx.counters()
+    assert int(counters.sum()) == 299
+    assert O.report_lines([s[0] for s in case["samples"]], counters) == report
+    ctx.close()
+
+
+@pytest.mark.parametrize("case", util.load_cases(), ids=lambda c: c["name"])
+def test_adversarial_cases_match_reference_and_oracle(case):
+    ctx, p = _ctx_for(case, max_stream_bytes=1 << 20, max_pairs=4096)
+    acc = [[bytearray(), bytearray()] for _ in range(p.nbins)]
+    for ch in util.case_chunks(case):
+        ref = O.demux_batch(p, ch, last=True)
+        r = ctx.run(ch, last=True)
+        _assert_same(r, ref, p.nbins, case["name"])
+        for b in range(p.nbins):
+            acc[b][0] += r.bin_bytes(0, b)
+            acc[b][1] += r.bin_bytes(1, b)
+    names = O.bin_names([s[0] for s in case["samples"]])
+    got = util.files_from_bins(names, acc)
+    exp = util.expected_files(case)
+    assert sorted(got) == sorted(exp)
+    for f in exp:
+        assert got[f] == exp[f], f
+    assert O.report_lines([s[0] for s in case["samples"]], ctx.counters()) == case["expect"]["report"]
+    ctx.close()
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg3", "cfg4", "cfg5"])
+def test_synthetic_configs_match_oracle(name):
+    from quade_b200.synth import Synth
+    s = Synth.from_config(name)
+    n = 50000
+    streams = s.generate(0, n)
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    ref = O.demux_batch(p, streams, last=True)
+    ctx, _ = _ctx_for(p, max_stream_bytes=32 << 20, max_pairs=n + 16)
+    r = ctx.run(streams, last=True)
+    _assert_same(r, ref, p.nbins, name)
+    assert r.n_pairs == n
+    ctx.close()
+
+
+def test_batched_with_carry_over_matches_one_shot():
+    """A chunk fed in ragged byte batches (double-buffered submit/collect) gives the same bins."""
+    from quade_b200.synth import Synth
+    s = Synth.from_config("cfg3")
+    n = 30000
+    streams = [bytes(a) for a in s.generate(7, n)]
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    ref = O.demux_batch(p, streams, last=True)
+    ctx, _ = _ctx_for(p, max_stream_bytes=4 << 20, max_pairs=16384)
+    rng = np.random.default_rng(3)
+    pos = [0] * 4
+    acc = [[bytearray(), bytearray()] for _ in range(p.nbins)]
+    total = 0
+    while True:
+        take = [min(len(streams[k]) - pos[k], int(rng.integers(100_000, 3_000_000)) // (1 if k < 2 else 4)) for k in range(4)]
+        last = all(pos[k] + take[k] == len(streams[k]) for k in range(4))
+        r = ctx.run([streams[k][pos[k]:pos[k] + take[k]] for k in range(4)], last=last)
+        total += r.n_pairs
+        for b in range(p.nbins):
+            acc[b][0] += r.bin_bytes(0, b)
+            acc[b][1] += r.bin_bytes(1, b)
+        for k in range(4):
+            pos[k] += r.consumed[k]
+        if last:
+            break
+    assert total == ref.n_pairs == n
+    assert (ctx.counters() == ref.counters).all()
+    for b in range(p.nbins):
+        assert bytes(acc[b][0]) == ref.bin_bytes(0, b) and bytes(acc[b][1]) == ref.bin_bytes(1, b)
+    ctx.close()
+
+
+def test_blank_header_is_fatal():
+    from quade_b200 import DemuxContext, QuadeError
+    ctx = DemuxContext(True, [(0, 4), (0, 4), (0, 0), (0, 0)], 0, ["ACAGACAG"], max_stream_bytes=1 << 16, max_pairs=64)
+    good = b"@a\nACGT\n+\nIIII\n"
+    with pytest.raises(QuadeError) as e:
+        ctx.run([b"@\nACGT\n+\nIIII\n", good, good, good])
+    assert e.value.code == -1
+    r = ctx.run([good, good, good, good])        # the context stays usable
+    assert r.n_pairs == 1
+    ctx.close()
+
+
+def test_empty_and_tiny_batches():
+    from quade_b200 import DemuxContext
+    ctx = DemuxContext(False, [(0, 4), (0, 0), (0, 0), (0, 0)], 10, ["ACAG"], max_stream_bytes=1 << 16, max_pairs=64)
+    p = O.OracleParams(False, [(0, 4), (0, 0), (0, 0), (0, 0)], 10, ["ACAG"])
+    for streams in ([b"", b"", b""], [b"@a\nAC\n+\nII", b"@a\nAC\n+\nII\n", b"@a\nACAG\n+\nIII5"],
+                    [b"@a\nAC\n+\nII\n", b"", b"@a\nACAG\n+\nIIII\n"]):
+        ref = O.demux_batch(p, streams, last=True)
+        _assert_same(ctx.run(streams, last=True), ref, p.nbins, repr(streams))
+        ref = O.demux_batch(p, streams, last=False)
+        _assert_same(ctx.run(streams, last=False), ref, p.nbins, repr(streams))
+    ctx.close()
