@@ -256,8 +256,8 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
         delete c;
         return fail(QUADE_ERR_ARG, "batch capacity too large: stream bytes and output arena must stay below 4 GiB");
     }
-    uint32_t ppb = 2048;
-    while (ppb < 4u * (uint32_t)c->n_bins && ppb < 65536u) ppb <<= 1;
+    uint32_t ppb = 1024;   // pairs per histogram block: small blocks balance the persistent CTAs
+    while (ppb < (uint32_t)c->n_bins && ppb < 65536u) ppb <<= 1;
     c->pairs_per_block = ppb;
     c->cap_blocks = (uint32_t)((c->cap_pairs + ppb - 1) / ppb);
     c->cumulative.assign(c->n_bins, 0);

@@ -40,12 +40,31 @@ __device__ __forceinline__ void st_status(u64 *p, u64 v)
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// one 0/1 bit per byte of a 32-bit word out of a 0x00/0xff byte mask
-__device__ __forceinline__ uint32_t bits4(uint32_t m) { return ((m & 0x08040201u) * 0x01010101u) >> 24; }
-__device__ __forceinline__ uint32_t nl_bits(uint32_t w) { return bits4(__vcmpeq4(w, 0x0a0a0a0au)); }
-__device__ __forceinline__ uint32_t ws_bits(uint32_t w)
+// SWAR byte classification, exact for all 256 byte values: 0x80 in every byte of w that is '\n' (nl) / Python-2
+// whitespace " \t\n\v\f\r" (ws).  The 7-bit adds cannot carry across bytes.
+__device__ __forceinline__ void word_flags(uint32_t w, uint32_t &nl, uint32_t &ws)
 {
-    return bits4(__vcmpeq4(w, 0x20202020u) | __vcmpleu4(__vsub4(w, 0x09090909u), 0x04040404u));
+    const uint32_t a = w & 0x7f7f7f7fu, lo = ~w & 0x80808080u;
+    const uint32_t ge9 = a + 0x77777777u, ge10 = a + 0x76767676u, ge11 = a + 0x75757575u, ge14 = a + 0x72727272u;
+    const uint32_t ge32 = a + 0x60606060u, ge33 = a + 0x5f5f5f5fu;
+    nl = ge10 & ~ge11 & lo;
+    ws = ((ge9 & ~ge14) | (ge32 & ~ge33)) & lo;
+}
+// the eight 0x80 flags of two words -> 8 bits (byte i of f0 -> bit i, byte i of f1 -> bit 4+i); the partial
+// products of the multiply land on distinct bit positions, so there are no carries
+__device__ __forceinline__ uint32_t gather8(uint32_t f0, uint32_t f1)
+{
+    return ((((f0 >> 7) | (f1 >> 3)) * 0x00204081u) >> 21) & 0xffu;
+}
+__device__ __forceinline__ void vector_masks(const int4 q, uint32_t &nlm, uint32_t &wsm)
+{
+    uint32_t n0, n1, n2, n3, w0, w1, w2, w3;
+    word_flags((uint32_t)q.x, n0, w0);
+    word_flags((uint32_t)q.y, n1, w1);
+    word_flags((uint32_t)q.z, n2, w2);
+    word_flags((uint32_t)q.w, n3, w3);
+    nlm = gather8(n0, n1) | gather8(n2, n3) << 8;
+    wsm = gather8(w0, w1) | gather8(w2, w3) << 8;
 }
 
 // Decoupled look-back: exclusive prefix of `total` over the tiles of one sequence.  Called by warp 0 only.
@@ -202,25 +221,40 @@ __global__ void __launch_bounds__(FT) k_frame(const __grid_constant__ BatchDev b
         const uint32_t n = st.n;
         const uint32_t tbase = (uint32_t)lt * (uint32_t)kFrameTile;
         const uint8_t *data = st.data;
-        const bool vnl = b.last && n > 0 && data[n - 1] != '\n'; // final line without '\n' still is a line
 
         // 1. coalesced 128-bit loads -> per-vector newline / whitespace bit masks in shared memory
-        for (int v = tid; v < FVEC + FHV; v += FT) {
-            const u64 pos = (u64)tbase + (u64)v * 16u;
-            uint32_t nlm = 0, wsm = 0xffffu;
-            if (pos < (((u64)n + 15u) & ~15ull)) {
-                int4 q = ld_stream_v4(data + pos);
-                nlm = nl_bits(q.x) | nl_bits(q.y) << 4 | nl_bits(q.z) << 8 | nl_bits(q.w) << 12;
-                wsm = ws_bits(q.x) | ws_bits(q.y) << 4 | ws_bits(q.z) << 8 | ws_bits(q.w) << 12;
-                if (pos + 16u > n) { // bytes past the end count as blanks
-                    uint32_t keep = (1u << (uint32_t)(n - pos)) - 1u;
-                    nlm &= keep;
-                    wsm |= ~keep & 0xffffu;
-                }
+        if ((u64)tbase + FBITS + 16u <= (u64)n) {        // tile and halo entirely inside the buffer
+#pragma unroll
+            for (int i = 0; i < FVEC / FT; ++i) {
+                const int v = i * FT + tid;
+                uint32_t nlm, wsm;
+                vector_masks(ld_stream_v4(data + (size_t)tbase + (size_t)v * 16u), nlm, wsm);
+                s_nl[v] = (uint16_t)nlm;
+                s_ws[v] = (uint16_t)wsm;
             }
-            if (vnl && (u64)n >= pos && (u64)n < pos + 16u) nlm |= 1u << (uint32_t)(n - pos);
-            s_nl[v] = (uint16_t)nlm;
-            s_ws[v] = (uint16_t)wsm;
+            if (tid < FHV) {
+                uint32_t nlm, wsm;
+                vector_masks(ld_stream_v4(data + (size_t)tbase + (size_t)(FVEC + tid) * 16u), nlm, wsm);
+                s_nl[FVEC + tid] = (uint16_t)nlm;
+                s_ws[FVEC + tid] = (uint16_t)wsm;
+            }
+        } else {
+            const bool vnl = b.last && n > 0 && data[n - 1] != '\n'; // final line without '\n' still is a line
+            for (int v = tid; v < FVEC + FHV; v += FT) {
+                const u64 pos = (u64)tbase + (u64)v * 16u;
+                uint32_t nlm = 0, wsm = 0xffffu;
+                if (pos < (((u64)n + 15u) & ~15ull)) {
+                    vector_masks(ld_stream_v4(data + pos), nlm, wsm);
+                    if (pos + 16u > n) { // bytes past the end count as blanks
+                        uint32_t keep = (1u << (uint32_t)(n - pos)) - 1u;
+                        nlm &= keep;
+                        wsm |= ~keep & 0xffffu;
+                    }
+                }
+                if (vnl && (u64)n >= pos && (u64)n < pos + 16u) nlm |= 1u << (uint32_t)(n - pos);
+                s_nl[v] = (uint16_t)nlm;
+                s_ws[v] = (uint16_t)wsm;
+            }
         }
         __syncthreads();
 
@@ -278,3 +312,5 @@ __global__ void __launch_bounds__(FT) k_frame(const __grid_constant__ BatchDev b
 
 #include "quade_kernels2.cuh"
 #include "quade_kernels3.cuh"
+#include "quade_compact.cuh"
+#include "quade_launch.cuh"

@@ -126,35 +126,40 @@ __device__ __forceinline__ void clamp_span(const int sp[2], uint32_t L, uint32_t
     *n = e > s ? e - s : 0u;
 }
 
-__global__ void __launch_bounds__(256) k_classify(const __grid_constant__ BatchDev b, int table_in_smem)
+constexpr int CT = 1024;   // threads per classify CTA: 128 pairs in flight, full occupancy with 2 CTAs per SM
+
+__global__ void __launch_bounds__(CT) k_classify(const __grid_constant__ BatchDev b, int table_in_smem)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    const uint32_t n_pairs = b.state->n_pairs;
-    const uint32_t p0 = blockIdx.x * b.pairs_per_block;
-    if (p0 >= n_pairs) return;
+    const uint32_t n_pairs = b.state->n_pairs, n_blocks = b.state->n_blocks;
+    if (blockIdx.x >= n_blocks) return;
     const int tid = threadIdx.x, nb = b.n_bins;
     uint32_t *h_b1 = reinterpret_cast<uint32_t *>(smem), *h_b2 = h_b1 + nb, *h_cnt = h_b2 + nb;
     const uint32_t n_slots = b.table.n_slots_mask + 1u, n_buckets = b.table.n_buckets_mask + 1u;
     const uint4 *entries = b.table.entries;
     const uint16_t *disp = b.table.disp;
-    for (int i = tid; i < 3 * nb; i += 256) h_b1[i] = 0u;
+    for (int i = tid; i < nb; i += CT) h_cnt[i] = 0u;
     if (table_in_smem) {
         uint4 *se = reinterpret_cast<uint4 *>(smem + (((size_t)3 * nb * 4 + 15) & ~(size_t)15));
         uint16_t *sd = reinterpret_cast<uint16_t *>(se + n_slots);
-        for (uint32_t i = tid; i < n_slots; i += 256) se[i] = entries[i];
-        for (uint32_t i = tid; i < n_buckets; i += 256) sd[i] = disp[i];
+        for (uint32_t i = tid; i < n_slots; i += CT) se[i] = entries[i];
+        for (uint32_t i = tid; i < n_buckets; i += CT) sd[i] = disp[i];
         entries = se;
         disp = sd;
     }
-    __syncthreads();
 
     const int gl = tid & 7, lane = tid & 31;
     const unsigned gmask = 0xffu << (lane & 24);
     const uint8_t *d1 = b.st[2].data, *d2 = b.dual ? b.st[3].data : nullptr;
+
+    for (uint32_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+    for (int i = tid; i < 2 * nb; i += CT) h_b1[i] = 0u;
+    __syncthreads();
+    const uint32_t p0 = blk * b.pairs_per_block;
     uint32_t end = p0 + b.pairs_per_block;
     if (end > n_pairs) end = n_pairs;
 
-    for (uint32_t p = p0 + (tid >> 3); p < end; p += 32) {
+    for (uint32_t p = p0 + (tid >> 3); p < end; p += CT / 8) {
         const uint4 r1 = b.st[2].rec[p];
         uint4 r2 = make_uint4(0, 0, 0, 0);
         if (b.dual) r2 = b.st[3].rec[p];
@@ -243,9 +248,11 @@ __global__ void __launch_bounds__(256) k_classify(const __grid_constant__ BatchD
         }
     }
     __syncthreads();
-    uint32_t *hg = b.hist + (size_t)blockIdx.x * 2u * nb;
-    for (int i = tid; i < 2 * nb; i += 256) hg[i] = h_b1[i];
-    for (int i = tid; i < nb; i += 256) {
+    uint32_t *hg = b.hist + (size_t)blk * 2u * nb;
+    for (int i = tid; i < 2 * nb; i += CT) hg[i] = h_b1[i];
+    __syncthreads();
+    } // blocks
+    for (int i = tid; i < nb; i += CT) {
         const uint32_t c = h_cnt[i];
         if (c) atomicAdd(reinterpret_cast<u64 *>(b.counters) + i, (u64)c);
     }

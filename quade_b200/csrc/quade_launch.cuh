@@ -1,0 +1,108 @@
+// quade_launch.cuh -- kernel launchers (included by quade_kernels.cu)
+#pragma once
+
+namespace quade {
+// ------------------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------------------
+static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0;
+
+static void init_launch_config()
+{
+    if (g_sms) return;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_frame, k_frame, FT, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_validate, k_validate, 256, 0);
+    cudaFuncSetAttribute(k_compact, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCompactSmem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact, k_compact, KT, kCompactSmem);
+    if (g_occ_frame < 1) g_occ_frame = 1;
+    if (g_occ_validate < 1) g_occ_validate = 1;
+    if (g_occ_compact < 1) g_occ_compact = 1;
+}
+
+void launch_frame(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    const uint32_t total = b.frame_tile_start[b.n_streams];
+    if (!total) return;
+    uint32_t grid = (uint32_t)(g_sms * g_occ_frame);
+    if (grid > total) grid = total;
+    k_frame<<<grid, FT, 0, s>>>(b, total);
+}
+
+void launch_validate(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    uint32_t max_tiles = 1;
+    for (int i = 0; i < b.n_streams; ++i) {
+        uint32_t t = (b.st[i].cap_rec + kValidateTile - 1) / kValidateTile;
+        if (t > max_tiles) max_tiles = t;
+    }
+    uint32_t gx = (uint32_t)(g_sms * g_occ_validate) / (uint32_t)b.n_streams;
+    if (gx < 1) gx = 1;
+    if (gx > max_tiles) gx = max_tiles;
+    k_validate<<<dim3(gx, b.n_streams), 256, 0, s>>>(b);
+}
+
+void launch_pairing(const BatchDev &b, cudaStream_t s) { k_pairing<<<1, 32, 0, s>>>(b); }
+
+size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem)
+{
+    size_t hist = (((size_t)3 * b.n_bins * 4) + 15) & ~(size_t)15;
+    size_t table = (size_t)(b.table.n_slots_mask + 1) * 16 + (size_t)(b.table.n_buckets_mask + 1) * 2;
+    bool in = hist + table <= 96 * 1024;
+    if (table_in_smem) *table_in_smem = in;
+    return in ? hist + table : hist;
+}
+
+void launch_classify(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    bool in_smem;
+    size_t sm = classify_smem_bytes(b, &in_smem);
+    cudaFuncSetAttribute(k_classify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_classify, CT, sm);
+    if (occ < 1) occ = 1;
+    uint32_t grid = (uint32_t)(g_sms * occ);
+    if (grid > b.cap_blocks) grid = b.cap_blocks;
+    k_classify<<<grid, CT, sm, s>>>(b, in_smem ? 1 : 0);
+}
+
+void launch_binscan(const BatchDev &b, cudaStream_t s)
+{
+    const uint32_t width = 2u * (uint32_t)b.n_bins;
+    k_binscan_blocks<<<(width + 31) / 32, dim3(32, 32), 0, s>>>(b);
+    k_binscan_bins<<<1, 1024, 0, s>>>(b);
+}
+
+void launch_offsets(const BatchDev &b, cudaStream_t s)
+{
+    size_t sm = (size_t)2 * b.n_bins * 4;
+    cudaFuncSetAttribute(k_offsets, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    k_offsets<<<b.cap_blocks, 256, sm, s>>>(b);
+}
+
+void launch_compact(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    uint32_t grid = (uint32_t)(g_sms * g_occ_compact);
+    uint32_t need = (b.cap_pairs + 255) / 256;
+    if (need < 1) need = 1;
+    if (grid > need) grid = need;
+    k_compact<<<grid, KT, kCompactSmem, s>>>(b);
+}
+
+int kernel_launch_count(int stage)
+{
+    switch (stage) {
+    case 0: case 1: case 2: case 3: case 5: case 6: return 1;
+    case 4: return 2;
+    default: return 0;
+    }
+}
+
+} // namespace quade
+
