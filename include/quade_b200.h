@@ -67,6 +67,8 @@ typedef struct {
 
 #define QUADE_BATCH_LAST 1u   /* buffers end at end-of-file: a final line without '\n' still is a line and the
                                  leftovers are dropped (src/pyFastq/FastqReader.py:37,57-58) */
+#define QUADE_BATCH_EOF(s) (1u << (8 + (s))) /* the same for stream s only: the host sets it per stream while the
+                                 other files of the chunk still have data to stage */
 #define QUADE_BATCH_DEVICE 2u /* stream[] are DEVICE pointers (16-byte aligned); outputs stay on the device */
 
 typedef struct {

@@ -118,7 +118,11 @@ def demux_batch(params, streams, last=True):
     ptrs = (C.c_void_p * 4)(*[a.ctypes.data if a.size else None for a in arrs])
     nb = (C.c_uint64 * 4)(*[a.size for a in arrs])
     r = _Result()
-    rc = L.qo_demux_batch(C.byref(p), ptrs, nb, int(bool(last)), C.byref(r))
+    if isinstance(last, (list, tuple)):   # per-stream end-of-file flags
+        lastm = sum(1 << (8 + s) for s, e in enumerate(last) if e)
+    else:
+        lastm = int(bool(last))
+    rc = L.qo_demux_batch(C.byref(p), ptrs, nb, lastm, C.byref(r))
     try:
         if rc != 0:
             raise OracleError(rc)

@@ -199,7 +199,7 @@ int qo_demux_batch(const qo_params *p, const uint8_t *const stream[4], const uin
     if ((err = registry_build(&reg, p)) != QO_OK) goto done;
 
     cursor cur[4]; memset(cur, 0, sizeof(cur));
-    for (int s = 0; s < ns; s++) { cur[s].b = stream[s]; cur[s].n = nbytes[s]; cur[s].last = last; }
+    for (int s = 0; s < ns; s++) { cur[s].b = stream[s]; cur[s].n = nbytes[s]; cur[s].last = (last & 1) || ((last >> (8 + s)) & 1); }
 
     uint8_t keybuf[4096], molbuf[4096];
     for (;;) {                                         /* while True:  Quade.py:210 / :240 */

@@ -58,7 +58,8 @@ typedef struct {
 
 /* Demultiplex one batch of a chunk.  `last` != 0 means the buffers end at end-of-file: a final line
  * without '\n' counts as a line and the leftovers are dropped (FastqReader.py:37,57-58).  With last == 0
- * only '\n'-terminated lines are used and consumed[] tells the caller what to carry over. */
+ * only '\n'-terminated lines are used and consumed[] tells the caller what to carry over.  Bit 8+s of `last`
+ * marks end-of-file for stream s alone. */
 int qo_demux_batch(const qo_params *p, const uint8_t *const stream[4], const uint64_t nbytes[4], int last,
                    qo_result *res);
 void qo_result_free(qo_result *res);

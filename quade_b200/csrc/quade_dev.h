@@ -64,7 +64,7 @@ struct BatchDev {
     StreamDev st[kMaxStreams];
     int n_streams;
     int dual;
-    int last;
+    int last;                  // bit s: the buffer of stream s ends at end-of-file
     int span[4][2];
     int min_qual;
     int wr_und, wr_pass, wr_fail;

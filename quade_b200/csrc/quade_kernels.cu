@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(FT) k_frame(const __grid_constant__ BatchDev b
                 s_ws[FVEC + tid] = (uint16_t)wsm;
             }
         } else {
-            const bool vnl = b.last && n > 0 && data[n - 1] != '\n'; // final line without '\n' still is a line
+            const bool vnl = ((b.last >> s) & 1) && n > 0 && data[n - 1] != '\n'; // final line without '\n' still is a line
             for (int v = tid; v < FVEC + FHV; v += FT) {
                 const u64 pos = (u64)tbase + (u64)v * 16u;
                 uint32_t nlm = 0, wsm = 0xffffu;

@@ -36,6 +36,14 @@ class DemuxResult:
             return np.zeros(0, dtype=np.uint8)
         return np.ctypeslib.as_array(C.cast(self.out_ptr[read], C.POINTER(C.c_uint8)), (n,))
 
+    def bin_view(self, read, b):
+        """memoryview (no copy) of bin b of the R1 (read=0) / R2 (read=1) arena; valid until the slot is reused."""
+        o = self.bin_off[read]
+        lo, hi = int(o[b]), int(o[b + 1])
+        if hi == lo:
+            return memoryview(b"")
+        return memoryview(self.arena(read))[lo:hi]
+
     def bin_bytes(self, read, b):
         o = self.bin_off[read]
         return self.arena(read)[int(o[b]):int(o[b + 1])].tobytes()
@@ -94,6 +102,17 @@ class DemuxContext:
     def in_flight(self):
         return len(self._pending)
 
+    @staticmethod
+    def _flags(last):
+        """last: True/False for all streams, or one bool per stream (end-of-file reached for that file only)."""
+        if isinstance(last, (list, tuple)):
+            f = 0
+            for s, e in enumerate(last):
+                if e:
+                    f |= 1 << (8 + s)
+            return f
+        return _lib.BATCH_LAST if last else 0
+
     def submit(self, streams, last=True, ticket=0):
         """streams: 3 or 4 host buffers (bytes / numpy uint8 / pinned views): R1, R2, I1[, I2]."""
         bt = _lib.Batch()
@@ -105,7 +124,7 @@ class DemuxContext:
             keep.append(a)
             bt.stream[s] = a.ctypes.data if a.size else None
             bt.nbytes[s] = a.size
-        bt.flags = _lib.BATCH_LAST if last else 0
+        bt.flags = self._flags(last)
         bt.ticket = int(ticket)
         _lib.check(self._L.quade_submit(self._ctx, C.byref(bt)))
         self._pending.append((False, keep))
@@ -116,7 +135,7 @@ class DemuxContext:
         for s in range(self.n_streams):
             bt.stream[s] = int(ptrs[s]) if nbytes[s] else None
             bt.nbytes[s] = int(nbytes[s])
-        bt.flags = (_lib.BATCH_LAST if last else 0) | _lib.BATCH_DEVICE
+        bt.flags = self._flags(last) | _lib.BATCH_DEVICE
         bt.ticket = int(ticket)
         _lib.check(self._L.quade_submit(self._ctx, C.byref(bt)))
         self._pending.append((True, keepalive))

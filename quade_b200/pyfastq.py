@@ -1,0 +1,87 @@
+"""pyFastq's role in the B200 build: staging, not parsing.
+
+The reference's `FastqReader(path)` (src/pyFastq/FastqReader.py:25-58) is a generator that frames 4 lines per
+record and builds one FastqSeq per record on the CPU.  Here the framing, validation and slicing run on the GPU
+(k_frame / k_classify), so `FastqReader(path)` only does what is left for the host: open the file with the
+reference's rule (gzip iff the path ends in "gz", FastqReader.py:30) and move raw bytes into page-locked
+buffers that `quade_submit` copies to the device.  There is no per-record Python code and no CPU parser.
+"""
+import gzip
+import threading
+import queue
+
+import numpy as np
+
+
+class FastqReader:
+    """Byte stager over one FASTQ file.
+
+    readinto(arr) fills a numpy uint8 view (normally a slice of a PinnedBuffer) and returns the number of bytes
+    stored; `eof` turns True once the file is exhausted.  With prefetch=True a helper thread keeps decompressed
+    blocks ready so that inflating the next block overlaps the GPU work on the current batch.
+    """
+
+    BLOCK = 8 << 20
+
+    def __init__(self, fastq_file, prefetch=True, depth=4):
+        self.path = fastq_file
+        # same rule as the reference: FastqReader.py:30
+        self._fh = gzip.open(fastq_file, "rb") if fastq_file[-2:] == "gz" else open(fastq_file, "rb", buffering=0)
+        self.eof = False
+        self.bytes_read = 0
+        self._pending = None       # (memoryview, offset) of a block partly handed out
+        self._q = None
+        if prefetch:
+            self._q = queue.Queue(maxsize=depth)
+            self._t = threading.Thread(target=self._pump, daemon=True)
+            self._t.start()
+
+    def _pump(self):
+        try:
+            while True:
+                blk = self._fh.read(self.BLOCK)
+                self._q.put(blk)
+                if not blk:
+                    return
+        except Exception as e:  # surfaced by readinto() on the consumer side
+            self._q.put(e)
+
+    def _next_block(self):
+        if self._q is not None:
+            blk = self._q.get()
+            if isinstance(blk, Exception):
+                raise blk
+            return blk
+        return self._fh.read(self.BLOCK)
+
+    def readinto(self, arr):
+        """Fill `arr` (numpy uint8, C-contiguous) as far as the file allows; returns bytes written."""
+        want = int(arr.size)
+        done = 0
+        while done < want and not self.eof:
+            if self._pending is None:
+                blk = self._next_block()
+                if not blk:
+                    self.eof = True
+                    break
+                self._pending = (memoryview(blk), 0)
+            mv, off = self._pending
+            n = min(want - done, len(mv) - off)
+            arr[done:done + n] = np.frombuffer(mv[off:off + n], dtype=np.uint8)
+            done += n
+            off += n
+            self._pending = (mv, off) if off < len(mv) else None
+        self.bytes_read += done
+        return done
+
+    def close(self):
+        try:
+            self._fh.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()

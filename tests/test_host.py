@@ -1,0 +1,165 @@
+"""Host side of the drop-in: config grammar, Sample / FastqWriter object model, batching with carry-over, report,
+chunk sharding over ranks (gloo, world_size 2).  The device is replaced by tests.util.OracleEngine here (the
+GPU twin of the golden run is tests/test_gpu_host.py)."""
+import gzip
+import os
+import shutil
+import subprocess
+import sys
+
+import pytest
+
+from tests import util
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DATASET = os.path.join(util.GOLDEN, "quade_dataset")
+
+
+def _fresh():
+    from quade_b200.sample import Sample
+    from quade_b200.fastq_writer import FastqWriter
+    Sample.RESET()
+    FastqWriter.PART = None
+
+
+def _stage_dataset(tmp_path):
+    """tmp/dataset + tmp/result laid out like the reference's test/ directory (the template's relative paths)."""
+    shutil.copytree(os.path.join(DATASET, "dataset"), tmp_path / "dataset")
+    (tmp_path / "result").mkdir()
+    shutil.copy(os.path.join(DATASET, "result", "Quade_conf_file.txt"), tmp_path / "result" / "Quade_conf_file.txt")
+    return tmp_path / "result"
+
+
+def _check_golden_outputs(workdir):
+    _, _, exp, report = util.quade_dataset()
+    got = sorted(f for f in os.listdir(workdir) if f.endswith(".fastq.gz"))
+    assert got == sorted(exp)                      # same file set: no *_fail_* files, no leftover parts
+    for f in exp:
+        with gzip.open(os.path.join(workdir, f), "rb") as fh:
+            assert fh.read() == exp[f], f
+    with open(os.path.join(workdir, "Quade_report.csv"), newline="") as fh:
+        assert fh.readlines()[1:] == report
+
+
+def test_template_has_the_reference_values(tmp_path, monkeypatch):
+    from quade_b200.quade import Quade
+    from quade_b200.sample import Sample
+    _fresh()
+    wd = _stage_dataset(tmp_path)
+    monkeypatch.chdir(wd)
+    with pytest.raises(SystemExit) as e:
+        Quade(init_conf=True)
+    assert e.value.code == 0
+    q = Quade(conf_file="Quade_conf_file.txt")
+    ref = Quade.__new__(Quade)
+    _fresh()
+    shutil.copy(os.path.join(DATASET, "result", "Quade_conf_file.txt"), "golden_conf.txt")
+    ref.__init__(conf_file="golden_conf.txt")
+    for k in ("minimal_qual", "idx1", "idx2", "mol1", "mol2", "idx1_pos", "idx2_pos", "mol1_pos", "mol2_pos",
+              "seq_R1", "seq_R2", "index_R1", "index_R2"):
+        assert getattr(q, k) == getattr(ref, k), k
+    assert q.spans() == [(0, 4), (0, 4), (3, 6), (3, 6)]
+    assert [(s.name, s.index) for s in Sample.SAMPLE_LIST] == [("S1", "ACAGACAG"), ("S2", "CTTGCTTG")]
+    assert (Sample.WRITE_PASS, Sample.WRITE_FAIL, Sample.WRITE_UNDETERMINED, Sample.MIN_QUAL) == (True, True, True, 25)
+
+
+@pytest.mark.parametrize("batch_bytes", [1 << 20, 2500, 997])
+def test_golden_run_through_the_host_loop(tmp_path, monkeypatch, batch_bytes):
+    """The documented smoke test (README.md:67-72) through Quade.__call__: staging, ragged batches with
+    carry-over, per-stream end-of-file flags, lazy file creation, report."""
+    from quade_b200.quade import Quade
+    _fresh()
+    wd = _stage_dataset(tmp_path)
+    monkeypatch.chdir(wd)
+    monkeypatch.setattr(Quade, "ENGINE_FACTORY", util.OracleEngine)
+    monkeypatch.setattr(Quade, "BATCH_BYTES", batch_bytes)
+    q = Quade(conf_file="Quade_conf_file.txt")
+    assert q() == 0
+    _check_golden_outputs(wd)
+
+
+def test_config_errors_exit_1(tmp_path, monkeypatch, capsys):
+    from quade_b200.quade import Quade
+    wd = _stage_dataset(tmp_path)
+    monkeypatch.chdir(wd)
+    good = open("Quade_conf_file.txt").read()
+    cases = {
+        "missing option": (good.replace("minimal_qual : 25", ""), "Option or section missing"),
+        "bad value": (good.replace("minimal_qual : 25", "minimal_qual : 41"), "One of the value in the configuration file is not correct"),
+        "not an int": (good.replace("index1_end : 4", "index1_end : x"), "One of the value in the configuration file is not correct"),
+        "lower-case index": (good.replace("index1_seq : ACAG", "index1_seq : acag"), "Non canonical DNA base in index"),
+        "duplicate index": (good.replace("CTTG", "ACAG"), "Index is not unique"),
+        "unreadable file": (good.replace("../dataset/C2_R1.fastq.gz", "../dataset/nope.fastq.gz"), "One of the file is incorrect or unreadable"),
+        "ragged lists": (good.replace("../dataset/C3_R4.fastq.gz", ""), "have to contain the same number of files"),
+        "end before start": (good.replace("molecular2_end : 6", "molecular2_end : 2"), "One of the value in the configuration file is not correct"),
+    }
+    for name, (text, msg) in cases.items():
+        _fresh()
+        with open("bad.txt", "w") as fh:
+            fh.write(text)
+        with pytest.raises(SystemExit) as e:
+            Quade(conf_file="bad.txt")
+        assert e.value.code == 1, name
+        assert msg in capsys.readouterr().out, name
+    _fresh()
+    with pytest.raises(SystemExit) as e:
+        Quade(conf_file=None)
+    assert e.value.code == 1
+    assert "A path to the configuration file is mandatory" in capsys.readouterr().out
+
+
+def test_writer_object_model(tmp_path, monkeypatch):
+    from quade_b200.fastq_writer import FastqWriter
+    monkeypatch.chdir(tmp_path)
+    _fresh()
+    w = FastqWriter(name="X_pass")
+    assert (w.R1_fastq_name, w.R2_fastq_name, w.counter, w.buffer_size) == ("X_pass_R1.fastq.gz", "X_pass_R2.fastq.gz", -1, 20)
+    assert not os.path.exists(w.R1_fastq_name)                  # lazy creation (FastqWriter.py:55-57)
+    w(b"@a:AC\nAC\n+\nII\n", b"@a:AC\nGT\n+\nII\n")
+    assert os.path.exists(w.R1_fastq_name) and w.counter == 1
+    w(memoryview(b"@b:AC\nAC\n+\nII\n"), memoryview(b"@b:AC\nGT\n+\nII\n"))
+    w.flush_buffers()
+    assert w.counter == 0
+    assert gzip.open(w.R1_fastq_name).read() == b"@a:AC\nAC\n+\nII\n@b:AC\nAC\n+\nII\n"
+    assert gzip.open(w.R2_fastq_name).read() == b"@a:AC\nGT\n+\nII\n@b:AC\nGT\n+\nII\n"
+    with pytest.raises(TypeError):
+        w(object(), object())                                   # no per-record CPU serialisation
+
+
+def test_report_matches_oracle_formatter():
+    from quade_b200.sample import Sample
+    from oracle import oracle as O
+    _fresh()
+    Sample.CLASS_INIT(True, True, True, 25)
+    for n, i in (("A", "ACGT"), ("B", "TTTT"), ("C", "GGGG")):
+        Sample(n, i)
+    for counters in ([0, 0, 0, 0, 0, 0, 0], [5, 0, 0, 0, 0, 0, 0], [3, 7, 2, 0, 0, 1, 0], [247, 25, 0, 27, 0, 0, 0]):
+        Sample.SET_COUNTS(counters)
+        lines = ["\n"] + ["{}\t{}\n".format(d, v) for d, v in Sample.REPORT()]
+        assert lines == O.report_lines(["A", "B", "C"], counters)
+        assert Sample.COUNTS() == counters
+    with pytest.raises(TypeError):
+        Sample.FINDER("read1", "read2", "index")                # the per-record CPU form is not provided
+
+
+def test_sharded_run_world_size_2_gloo(tmp_path):
+    """Two ranks (gloo), chunks round-robin, counters all-reduced, parts merged in chunk order: same files and
+    report as the single-process run."""
+    wd = _stage_dataset(tmp_path)
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "from tests import util\n"
+        "from quade_b200.quade import Quade\n"
+        "Quade.ENGINE_FACTORY = util.OracleEngine\n"
+        "Quade.BATCH_BYTES = 4096\n"
+        "sys.exit(Quade(conf_file='Quade_conf_file.txt')())\n" % ROOT)
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT="29641")
+        procs.append(subprocess.Popen([sys.executable, "-c", code], cwd=str(wd), env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=240)[0] for p in procs]
+    assert [p.returncode for p in procs] == [0, 0], outs
+    _check_golden_outputs(wd)
+    assert "Start parsing chunk 2" in outs[1] and "Start parsing chunk 2" not in outs[0]

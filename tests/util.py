@@ -93,3 +93,34 @@ def quade_dataset():
                      "write_pass": True, "write_fail": True, "write_undetermined": True},
             "samples": [["S1", "ACAG", "ACAG"], ["S2", "CTTG", "CTTG"]]}
     return case, chunks, exp, report
+
+
+class OracleEngine:
+    """Stand-in for DemuxContext in CPU-only tests of the HOST logic (batching, carry-over, writers, sharding):
+    same run()/close() surface, answers computed by the oracle.  Test infrastructure only."""
+
+    class _Res:
+        def __init__(self, r):
+            self.n_pairs, self.consumed, self.n_skipped = r.n_pairs, list(r.consumed), list(r.n_skipped)
+            self.counters, self._r = r.counters, r
+
+        def bin_view(self, read, b):
+            return memoryview(self._r.bin_bytes(read, b))
+
+    def __init__(self, quade, device=0):
+        from quade_b200.sample import Sample
+        self.params = O.OracleParams(quade.idx2, quade.spans(), quade.minimal_qual, [s.index for s in Sample.SAMPLE_LIST],
+                                     Sample.WRITE_UNDETERMINED, Sample.WRITE_PASS, Sample.WRITE_FAIL)
+        self.batches = 0
+
+    def run(self, streams, last=True):
+        self.batches += 1
+        try:
+            return self._Res(O.demux_batch(self.params, [bytes(s) for s in streams], last=list(last) if isinstance(last, (list, tuple)) else last))
+        except O.OracleError as e:
+            err = RuntimeError("oracle error %d" % e.code)
+            err.code = e.code
+            raise err
+
+    def close(self):
+        pass
