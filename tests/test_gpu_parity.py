@@ -138,3 +138,31 @@ def test_empty_and_tiny_batches():
         ref = O.demux_batch(p, streams, last=False)
         _assert_same(ctx.run(streams, last=False), ref, p.nbins, repr(streams))
     ctx.close()
+
+
+def test_per_stream_eof_flags_match_oracle_batch_by_batch():
+    """Files of a chunk reach end-of-file in different batches (QUADE_BATCH_EOF(s)); the final record of every
+    file has no trailing newline.  Every batch result equals the oracle's."""
+    from quade_b200.synth import Synth
+    s = Synth.from_config("cfg3")
+    n = 6000
+    streams = [bytes(a)[:-1] for a in s.generate(11, n)]       # drop the last '\n' of every file
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    ctx, _ = _ctx_for(p, max_stream_bytes=1 << 20, max_pairs=8192)
+    rng = np.random.default_rng(5)
+    pos, avail, total = [0] * 4, [0] * 4, 0
+    for it in range(10000):
+        for k in range(4):
+            avail[k] = min(len(streams[k]), max(avail[k], pos[k]) + int(rng.integers(1000, 400_000)))
+        eof = [avail[k] == len(streams[k]) for k in range(4)]
+        batch = [streams[k][pos[k]:avail[k]] for k in range(4)]
+        ref = O.demux_batch(p, batch, last=eof)
+        r = ctx.run(batch, last=eof)
+        _assert_same(r, ref, p.nbins, "batch %d" % it)
+        total += r.n_pairs
+        for k in range(4):
+            pos[k] += r.consumed[k]
+        if all(eof):
+            break
+    assert total == n
+    ctx.close()
