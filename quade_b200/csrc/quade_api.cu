@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -250,7 +251,7 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->cap_pairs = p->max_pairs ? p->max_pairs : c->cap_bytes / 64;
     if (c->cap_pairs < 32) c->cap_pairs = 32;
     c->cap_rec = c->cap_pairs + c->cap_pairs / 8 + 1024;
-    c->suf_cap = (width + 3 + 3) & ~3u;
+    c->suf_cap = (width + 3 + 15) & ~15u;   // 16-byte slots: k_compact3 stages them with 128-bit loads
     c->out_cap = c->cap_bytes + c->cap_pairs * c->suf_cap;
     if (c->cap_bytes > kMaxStreamBytes || c->out_cap >= (1ull << 32) || c->cap_rec * 4 >= (1ull << 32)) {
         delete c;
@@ -261,6 +262,7 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->pairs_per_block = ppb;
     c->cap_blocks = (uint32_t)((c->cap_pairs + ppb - 1) / ppb);
     c->cumulative.assign(c->n_bins, 0);
+    if (const char *v = getenv("QUADE_COMPACT")) set_compact_variant(atoi(v));
     int rc = QUADE_OK;
     if (cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking) != cudaSuccess ||

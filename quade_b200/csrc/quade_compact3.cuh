@@ -1,0 +1,292 @@
+// quade_compact3.cuh -- K5 compact, TMA-staged (included by quade_kernels.cu)
+//
+//   '@' name ':' index [':' molecular] '\n' seq '\n' '+' '\n' qual '\n'      (FastqWriter.py:61-69, FastqSeq.py:76-82)
+//
+// One warp (= one CTA) owns tiles of `tp` (<= 8) consecutive pairs = 2*tp records.  The raw bytes of the tile's
+// R1 records and of its R2 records are each ONE contiguous span of the input (pairs are in input order), so
+// they are staged with two cp.async.bulk (TMA) copies per tile into a two-stage shared-memory ring, signalled
+// through an mbarrier; the copy of tile t+1 is in flight while tile t is assembled.
+//
+// Phase 1 (dense, lane = record x role): the variable part of the record -- '@' name suffix and the first
+// bytes of the sequence up to the next 16-byte boundary of the DESTINATION -- is composed word-wise into a
+// per-record HEAD slot at destination alignment.
+// Phase 2 (one record per iteration, lane = 16-byte vector of the output): HEAD vectors are copied from the
+// slot, the rest (seq "\n+\n" qual "\n", contiguous in a clean input record) is funnel-shifted from the staged
+// span; aligned 128-bit stores, the first / last partial vector by bytes.
+// Records that are not clean (CRLF, decorated '+' line, trailing blanks, no final newline), too long for the
+// stage or with an oversized name take the generic byte path straight from global memory.
+#pragma once
+
+namespace quade {
+namespace {
+
+constexpr int C3_TP = 8;                  // pairs per tile (upper bound; the batch's value is in BatchState)
+constexpr int C3_CAP = 3072;              // staged bytes per stream per stage
+constexpr int C3_HS = 144;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
+constexpr int C3_SUFV = 4;                // staged suffix: up to 64 bytes per pair
+constexpr int C3_IN_BYTES = 2 * 2 * (C3_CAP + 32);
+constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * 16 + 32;
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ uint32_t lds32(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+// shared -> shared copy of n bytes, any alignment on both sides, full destination words by funnel shift
+__device__ __forceinline__ void seg_copy(uint32_t dst, uint32_t src, uint32_t n)
+{
+    uint32_t head = (4u - (dst & 3u)) & 3u;
+    head = head < n ? head : n;
+    for (uint32_t i = 0; i < head; ++i) sts8(dst + i, lds8(src + i));
+    dst += head;
+    src += head;
+    n -= head;
+    const uint32_t nw = n >> 2, sh = (src & 3u) * 8u;
+    uint32_t sa = src & ~3u;
+    uint32_t w0 = nw ? lds32(sa) : 0u;
+    for (uint32_t i = 0; i < nw; ++i) {
+        sa += 4u;
+        const uint32_t w1 = lds32(sa);
+        sts32(dst, __funnelshift_r(w0, w1, sh));
+        w0 = w1;
+        dst += 4u;
+    }
+    src += nw * 4u;
+    for (uint32_t i = 0; i < (n & 3u); ++i) sts8(dst + i, lds8(src + i));
+}
+
+// byte path straight from global memory: any record shape (the whole warp works on one record)
+__device__ __forceinline__ void emit_generic(const BatchDev &b, int k, uint32_t p, uint32_t cls, uint32_t ooff, int lane)
+{
+    const uint4 rc = b.st[k].rec[p];
+    const uint32_t nlen = b.st[k].vnlen[p], L = rc.w, suf_len = (cls >> 16) & 0xffu;
+    const uint8_t *sufp = b.suffix + (size_t)p * b.suf_cap, *data = b.st[k].data;
+    uint8_t *gout = b.out[k] + (size_t)ooff;
+    const uint32_t total = nlen + suf_len + 2u * L + 5u, D1 = 1u + nlen + suf_len, D2 = D1 + L + 3u;
+#pragma unroll 1
+    for (uint32_t x = lane; x < total; x += 32) {
+        uint32_t ch;
+        if (x == 0u) ch = '@';
+        else if (x < 1u + nlen) ch = data[rc.x + x - 1u];
+        else if (x < D1) ch = sufp[x - 1u - nlen];
+        else if (x < D1 + L) ch = data[rc.y + x - D1];
+        else if (x < D2) ch = (x - D1 - L == 1u) ? '+' : '\n';
+        else if (x < D2 + L) ch = data[rc.z + x - D2];
+        else ch = '\n';
+        gout[x] = (uint8_t)ch;
+    }
+}
+
+struct TileMeta {
+    uint4 rc;          // this lane's record {name_off, seq_off, qual_off, seq_len}
+    uint32_t nlen, cls, ooff;
+    uint32_t start0, start1, size0, size1;   // staged span per stream (uniform); size 0 = nothing staged
+    bool staged;                  // uniform: the spans fit the stage
+};
+
+__global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDev b)
+{
+    extern __shared__ __align__(128) uint8_t c3_smem[];
+    const BatchState *St = b.state;
+    if (St->err_capacity) return;
+    const int lane = threadIdx.x;
+    const uint32_t n_pairs = St->n_pairs;
+    uint32_t tp = St->compact_tp;
+    tp = tp < 1u ? 1u : (tp > (uint32_t)C3_TP ? (uint32_t)C3_TP : tp);
+    const uint32_t n_tiles = (n_pairs + tp - 1u) / tp;
+
+    const uint32_t sm0 = smem_u32(c3_smem);
+    const uint32_t s_in = sm0;                                         // [stage][stream][C3_CAP + 32]
+    const uint32_t s_head = s_in + C3_IN_BYTES;                        // [2*TP][C3_HS]
+    const uint32_t s_suf = s_head + 2 * C3_TP * C3_HS;                 // [TP][64]
+    const uint32_t s_par = s_suf + C3_TP * C3_SUFV * 16;               // [2*TP] uint4
+    const uint32_t s_bar = s_par + 2 * C3_TP * 16;                     // 2 mbarriers
+    if (lane == 0) {
+        mbar_init(s_bar, 1);
+        mbar_init(s_bar + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    const uint32_t r = lane & 15, role = lane >> 4;
+    const uint32_t k = r >= tp ? 1u : 0u, pr = r - k * tp;             // stream and pair slot of this lane's record
+    const bool rec_lane = r < 2u * tp;
+    const uint32_t sufv = b.suf_cap >> 4;                              // suffix slot = sufv 16-byte vectors
+
+    auto load_meta = [&](uint32_t tile, TileMeta &m) {
+        const uint32_t p = tile * tp + pr;
+        m.rc = make_uint4(0, 0, 0, 0);
+        m.nlen = m.cls = m.ooff = 0u;
+        if (rec_lane && tile < n_tiles && p < n_pairs) {
+            m.cls = b.cls[p];
+            if (m.cls >> 31) {
+                m.rc = b.st[k].rec[p];
+                m.nlen = b.st[k].vnlen[p];
+                m.ooff = k ? b.out2[p] : b.out1[p];
+            }
+        }
+        // span of each stream: first .. last written record of the tile (lanes of role 0 vote)
+        m.staged = true;
+#pragma unroll
+        for (int kk = 0; kk < 2; ++kk) {
+            const unsigned mine = __ballot_sync(0xffffffffu, role == 0u && rec_lane && k == (uint32_t)kk && (m.cls >> 31));
+            uint32_t start = 0, size = 0;
+            if (mine) {
+                const int lo = __ffs(mine) - 1, hi = 31 - __clz(mine);
+                const uint32_t first = __shfl_sync(0xffffffffu, m.rc.x, lo);
+                const uint32_t lz = __shfl_sync(0xffffffffu, m.rc.z, hi), lw = __shfl_sync(0xffffffffu, m.rc.w, hi);
+                start = first & ~15u;
+                uint32_t end = lz + lw + 1u;                            // one byte past the quality string
+                const uint32_t nmax = (b.st[kk].n + 15u) & ~15u;
+                end = (end + 15u) & ~15u;
+                end = end < nmax ? end : nmax;
+                size = end - start;
+                if (size > (uint32_t)C3_CAP) { m.staged = false; size = 0; }
+            }
+            if (kk == 0) { m.start0 = start; m.size0 = size; }
+            else { m.start1 = start; m.size1 = size; }
+        }
+        if (!m.staged) m.size0 = m.size1 = 0;
+    };
+    auto issue = [&](const TileMeta &m, uint32_t stage) {
+        if (lane == 0 && (m.size0 | m.size1)) {
+            const uint32_t bar = s_bar + 8u * stage;
+            fence_proxy_async();
+            mbar_expect_tx(bar, m.size0 + m.size1);
+            if (m.size0) bulk_g2s(s_in + (stage * 2u + 0u) * (C3_CAP + 32) + 16u, b.st[0].data + m.start0, m.size0, bar);
+            if (m.size1) bulk_g2s(s_in + (stage * 2u + 1u) * (C3_CAP + 32) + 16u, b.st[1].data + m.start1, m.size1, bar);
+        }
+    };
+
+    uint32_t phase_bits = 0;
+    uint32_t tile = blockIdx.x, it = 0;
+    TileMeta cur, nxt;
+    if (tile < n_tiles) {
+        load_meta(tile, cur);
+        issue(cur, 0);
+    }
+#pragma unroll 1
+    for (; tile < n_tiles; tile += gridDim.x, ++it) {
+        const uint32_t stage = it & 1u;
+        const uint32_t ntile = tile + gridDim.x;
+        if (ntile < n_tiles) {
+            load_meta(ntile, nxt);
+            issue(nxt, stage ^ 1u);
+        }
+        if (cur.size0 | cur.size1) {
+            const uint32_t bar = s_bar + 8u * stage;
+            while (!mbar_try_wait(bar, (phase_bits >> stage) & 1u)) {}
+            phase_bits ^= 1u << stage;
+        }
+
+        // ---------------- phase 1: HEAD slots ----------------
+        const uint32_t p = tile * tp + pr;
+        const bool written = rec_lane && (cur.cls >> 31);
+        const uint32_t L = cur.rc.w, nlen = cur.nlen, suf_len = (cur.cls >> 16) & 0xffu;
+        const uint32_t total = nlen + suf_len + 2u * L + 5u, D1 = 1u + nlen + suf_len;
+        const uint32_t a = cur.ooff & 15u;
+        uint32_t J = ((a + D1 + 15u) & ~15u) - a;
+        J = J < total ? J : total;
+        // smem address of global byte g of this lane's stream: sbase + g
+        const uint32_t sbase = s_in + (stage * 2u + k) * (C3_CAP + 32) + 16u - (k ? cur.start1 : cur.start0);
+        bool fast = written && cur.staged && (cur.rc.z - cur.rc.y == L + 3u) && (a + J <= (uint32_t)C3_HS) &&
+                    total < (1u << 20) && suf_len <= (sufv < (uint32_t)C3_SUFV ? sufv : (uint32_t)C3_SUFV) * 16u && (cur.rc.z + L < b.st[k].n);
+        if (fast) fast = lds8(sbase + cur.rc.y + L + 1u) == '+' && lds8(sbase + cur.rc.z + L) == '\n';
+        // stage the pair's suffix (one copy per pair, by the R1 lanes of role 0)
+        if (role == 0u && k == 0u && written) {
+            const uint4 *sp = reinterpret_cast<const uint4 *>(b.suffix + (size_t)p * b.suf_cap);
+            for (uint32_t v = 0; v < sufv && v < (uint32_t)C3_SUFV; ++v) sts128(s_suf + (pr * C3_SUFV + v) * 16u, sp[v]);
+        }
+        __syncwarp();
+        const uint32_t hs = s_head + r * C3_HS;
+        if (fast) {
+            uint32_t d1, s1, n1, d2 = 0, s2 = 0, n2 = 0;
+            if (role == 0u) {                      // '@' name
+                sts8(hs + a, '@');
+                d1 = hs + a + 1u; s1 = sbase + cur.rc.x; n1 = nlen;
+            } else {                               // suffix, then the sequence bytes up to the vector boundary
+                d1 = hs + a + 1u + nlen; s1 = s_suf + pr * C3_SUFV * 16u; n1 = suf_len;
+                d2 = hs + a + D1; s2 = sbase + cur.rc.y; n2 = J - D1;
+            }
+            seg_copy(d1, s1, n1);
+            seg_copy(d2, s2, n2);
+        }
+        if (role == 0u && rec_lane) {
+            // srcB + x = smem address of output byte x (x >= D1) in the staged span
+            const uint32_t flags = (written ? 1u : 0u) | (fast ? 2u : 0u);
+            sts128(s_par + r * 16u, make_uint4(cur.ooff, total | J << 20, sbase + cur.rc.y - D1, flags | cur.cls << 2));
+        }
+        __syncwarp();
+
+        // ---------------- phase 2: one record per iteration ----------------
+        const uint32_t nrec = 2u * tp;
+#pragma unroll 1
+        for (uint32_t i = 0; i < nrec; ++i) {
+            const uint4 P = lds128(s_par + i * 16u);
+            if (!(P.w & 1u)) continue;
+            const uint32_t kk = i >= tp ? 1u : 0u;
+            if (!(P.w & 2u)) {
+                const uint32_t pp = tile * tp + (i - kk * tp);
+                emit_generic(b, (int)kk, pp, b.cls[pp], P.x, lane);
+                continue;
+            }
+            const uint32_t tot = P.y & 0xfffffu, Ji = P.y >> 20, ai = P.x & 15u;
+            uint8_t *gdst = b.out[kk] + (size_t)(P.x - ai);
+            const uint32_t endb = ai + tot, F0 = ai ? 1u : 0u, F1 = endb >> 4, vJ = (ai + Ji) >> 4;
+            const uint32_t hsi = s_head + i * C3_HS;
+            const uint32_t srcb = P.z - ai;                 // + y = smem address of byte y of the aligned frame
+            const uint32_t sr = srcb & 15u;
+#pragma unroll 1
+            for (uint32_t v = lane; v < F1; v += 32) {
+                if (v < F0) continue;
+                uint4 val;
+                if (v < vJ) val = lds128(hsi + 16u * v);
+                else {
+                    const uint32_t sa = (srcb + 16u * v) & ~15u;
+                    val = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
+                }
+                *reinterpret_cast<uint4 *>(gdst + 16u * v) = val;
+            }
+            // first partial vector: bytes [ai, min(16, endb)); last partial vector: [16*F1, endb)
+            uint32_t y = 0xffffffffu;
+            if (lane < 16) {
+                if (ai && (uint32_t)lane >= ai && (uint32_t)lane < endb) y = lane;
+            } else {
+                const uint32_t t = 16u * F1 + (lane - 16);
+                if (t < endb && (F1 > 0u || ai == 0u)) y = t;
+            }
+            if (y != 0xffffffffu) gdst[y] = (uint8_t)(y < ai + Ji ? lds8(hsi + y) : lds8(srcb + y));
+        }
+        __syncwarp();
+        cur = nxt;
+    }
+}
+
+} // namespace
+} // namespace quade

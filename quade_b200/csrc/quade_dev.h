@@ -36,7 +36,7 @@ struct BatchState {
     uint32_t err_blank;                // blank header inside the parsed range
     uint32_t ticket_frame;             // dynamic tile counters
     uint32_t ticket_validate[kMaxStreams];
-    uint32_t pad;
+    uint32_t compact_tp;               // pairs per k_compact3 tile, from the mean record size (k_pairing)
     unsigned long long out_total[2];   // bytes of the R1 / R2 arenas
 };
 
@@ -72,7 +72,7 @@ struct BatchDev {
     uint32_t cap_pairs;
     uint32_t pairs_per_block;
     uint32_t cap_blocks;
-    uint32_t suf_cap;          // bytes per suffix slot (multiple of 4)
+    uint32_t suf_cap;          // bytes per suffix slot (multiple of 16)
     unsigned long long out_cap[2];
     BatchState *state;
     HashTable table;
@@ -112,6 +112,7 @@ void launch_classify(const BatchDev &b, cudaStream_t s);
 void launch_binscan(const BatchDev &b, cudaStream_t s);
 void launch_offsets(const BatchDev &b, cudaStream_t s);
 void launch_compact(const BatchDev &b, cudaStream_t s);
+void set_compact_variant(int v);   // 3 = TMA-staged k_compact3 (default), 2 = cp.async k_compact
 int kernel_launch_count(int stage);
 size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
 

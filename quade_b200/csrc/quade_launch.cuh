@@ -5,7 +5,8 @@ namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------------------
-static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0;
+static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 2;
+void set_compact_variant(int v) { g_compact_variant = v; }
 
 static void init_launch_config()
 {
@@ -20,6 +21,9 @@ static void init_launch_config()
     if (g_occ_frame < 1) g_occ_frame = 1;
     if (g_occ_validate < 1) g_occ_validate = 1;
     if (g_occ_compact < 1) g_occ_compact = 1;
+    cudaFuncSetAttribute(k_compact3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact3, k_compact3, 32, C3_SMEM);
+    if (g_occ_compact3 < 1) g_occ_compact3 = 1;
 }
 
 void launch_frame(const BatchDev &b, cudaStream_t s)
@@ -88,6 +92,13 @@ void launch_offsets(const BatchDev &b, cudaStream_t s)
 void launch_compact(const BatchDev &b, cudaStream_t s)
 {
     init_launch_config();
+    if (g_compact_variant == 3) {
+        uint32_t grid3 = (uint32_t)(g_sms * g_occ_compact3);
+        if (grid3 > b.cap_pairs) grid3 = b.cap_pairs;
+        if (grid3 < 1) grid3 = 1;
+        k_compact3<<<grid3, 32, C3_SMEM, s>>>(b);
+        return;
+    }
     uint32_t grid = (uint32_t)(g_sms * g_occ_compact);
     uint32_t need = (b.cap_pairs + 255) / 256;
     if (need < 1) need = 1;
