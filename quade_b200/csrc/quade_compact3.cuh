@@ -22,9 +22,10 @@ namespace {
 
 constexpr int C3_TP = 8;                  // pairs per tile (upper bound; the batch's value is in BatchState)
 constexpr int C3_CAP = 3072;              // staged bytes per stream per stage
-constexpr int C3_HS = 144;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
+constexpr int C3_HS = 176;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
 constexpr int C3_SUFV = 4;                // staged suffix: up to 64 bytes per pair
-constexpr int C3_IN_BYTES = 2 * 2 * (C3_CAP + 32);
+constexpr int C3_STAGES = 1;               // 1: more resident warps hide the copy latency; 2: per-warp prefetch
+constexpr int C3_IN_BYTES = C3_STAGES * 2 * (C3_CAP + 32);
 constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * 16 + 32;
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
@@ -193,11 +194,11 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
     }
 #pragma unroll 1
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
-        const uint32_t stage = it & 1u;
+        const uint32_t stage = C3_STAGES == 2 ? (it & 1u) : 0u;
         const uint32_t ntile = tile + gridDim.x;
         if (ntile < n_tiles) {
             load_meta(ntile, nxt);
-            issue(nxt, stage ^ 1u);
+            if (C3_STAGES == 2) issue(nxt, stage ^ 1u);
         }
         if (cur.size0 | cur.size1) {
             const uint32_t bar = s_bar + 8u * stage;
@@ -215,7 +216,12 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
         J = J < total ? J : total;
         // smem address of global byte g of this lane's stream: sbase + g
         const uint32_t sbase = s_in + (stage * 2u + k) * (C3_CAP + 32) + 16u - (k ? cur.start1 : cur.start0);
-        bool fast = written && cur.staged && (cur.rc.z - cur.rc.y == L + 3u) && (a + J <= (uint32_t)C3_HS) &&
+        // srcb + y = smem address, in the staged span, of byte y of the record's 16-byte aligned output frame
+        // (y = a + x for output byte x >= D1).  The HEAD slot is laid out with the SAME residue mod 16
+        // (hb + y, hb = slot + (srcb & 15)), so that phase 2 shifts every vector of the record alike.
+        const uint32_t srcb = sbase + cur.rc.y - D1 - a;
+        const uint32_t hb = s_head + r * C3_HS + (srcb & 15u);
+        bool fast = written && cur.staged && (cur.rc.z - cur.rc.y == L + 3u) && (15u + a + J <= (uint32_t)C3_HS) &&
                     total < (1u << 20) && suf_len <= (sufv < (uint32_t)C3_SUFV ? sufv : (uint32_t)C3_SUFV) * 16u && (cur.rc.z + L < b.st[k].n);
         if (fast) fast = lds8(sbase + cur.rc.y + L + 1u) == '+' && lds8(sbase + cur.rc.z + L) == '\n';
         // stage the pair's suffix (one copy per pair, by the R1 lanes of role 0)
@@ -224,66 +230,67 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
             for (uint32_t v = 0; v < sufv && v < (uint32_t)C3_SUFV; ++v) sts128(s_suf + (pr * C3_SUFV + v) * 16u, sp[v]);
         }
         __syncwarp();
-        const uint32_t hs = s_head + r * C3_HS;
         if (fast) {
             uint32_t d1, s1, n1, d2 = 0, s2 = 0, n2 = 0;
             if (role == 0u) {                      // '@' name
-                sts8(hs + a, '@');
-                d1 = hs + a + 1u; s1 = sbase + cur.rc.x; n1 = nlen;
+                sts8(hb + a, '@');
+                d1 = hb + a + 1u; s1 = sbase + cur.rc.x; n1 = nlen;
             } else {                               // suffix, then the sequence bytes up to the vector boundary
-                d1 = hs + a + 1u + nlen; s1 = s_suf + pr * C3_SUFV * 16u; n1 = suf_len;
-                d2 = hs + a + D1; s2 = sbase + cur.rc.y; n2 = J - D1;
+                d1 = hb + a + 1u + nlen; s1 = s_suf + pr * C3_SUFV * 16u; n1 = suf_len;
+                d2 = hb + a + D1; s2 = sbase + cur.rc.y; n2 = J - D1;
             }
             seg_copy(d1, s1, n1);
             seg_copy(d2, s2, n2);
         }
         if (role == 0u && rec_lane) {
-            // srcB + x = smem address of output byte x (x >= D1) in the staged span
             const uint32_t flags = (written ? 1u : 0u) | (fast ? 2u : 0u);
-            sts128(s_par + r * 16u, make_uint4(cur.ooff, total | J << 20, sbase + cur.rc.y - D1, flags | cur.cls << 2));
+            sts128(s_par + r * 16u, fast ? make_uint4(cur.ooff, total | J << 20, srcb, flags) : make_uint4(cur.ooff, 0u, s_in, flags));
         }
+        const unsigned slow = __ballot_sync(0xffffffffu, role == 0u && written && !fast);
         __syncwarp();
 
-        // ---------------- phase 2: one record per iteration ----------------
+        // ---------------- phase 2: one record per iteration, branch-free ----------------
         const uint32_t nrec = 2u * tp;
-#pragma unroll 1
+#pragma unroll 2
         for (uint32_t i = 0; i < nrec; ++i) {
             const uint4 P = lds128(s_par + i * 16u);
-            if (!(P.w & 1u)) continue;
+            const bool act = (P.w & 3u) == 3u;
             const uint32_t kk = i >= tp ? 1u : 0u;
-            if (!(P.w & 2u)) {
-                const uint32_t pp = tile * tp + (i - kk * tp);
-                emit_generic(b, (int)kk, pp, b.cls[pp], P.x, lane);
-                continue;
-            }
             const uint32_t tot = P.y & 0xfffffu, Ji = P.y >> 20, ai = P.x & 15u;
             uint8_t *gdst = b.out[kk] + (size_t)(P.x - ai);
-            const uint32_t endb = ai + tot, F0 = ai ? 1u : 0u, F1 = endb >> 4, vJ = (ai + Ji) >> 4;
-            const uint32_t hsi = s_head + i * C3_HS;
-            const uint32_t srcb = P.z - ai;                 // + y = smem address of byte y of the aligned frame
-            const uint32_t sr = srcb & 15u;
+            const uint32_t endb = ai + tot, F1 = endb >> 4, hend = ai + Ji;      // hend: end of the HEAD part
+            const uint32_t sb = P.z, sr = sb & 15u;
+            const uint32_t hbi = s_head + i * C3_HS + sr;
+            {
+                const uint32_t v = lane, y0 = 16u * v;
+                const uint32_t sa = ((y0 < hend ? hbi : sb) + y0) & ~15u;
+                const uint4 val = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
+                if (act && v < F1 && (v > 0u || ai == 0u)) *reinterpret_cast<uint4 *>(gdst + y0) = val;
+            }
+            if (F1 > 32u && act) {                                                 // records longer than 512 bytes
 #pragma unroll 1
-            for (uint32_t v = lane; v < F1; v += 32) {
-                if (v < F0) continue;
-                uint4 val;
-                if (v < vJ) val = lds128(hsi + 16u * v);
-                else {
-                    const uint32_t sa = (srcb + 16u * v) & ~15u;
-                    val = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
+                for (uint32_t v = lane + 32u; v < F1; v += 32) {
+                    const uint32_t sa = (sb + 16u * v) & ~15u;
+                    *reinterpret_cast<uint4 *>(gdst + 16u * v) = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
                 }
-                *reinterpret_cast<uint4 *>(gdst + 16u * v) = val;
             }
-            // first partial vector: bytes [ai, min(16, endb)); last partial vector: [16*F1, endb)
-            uint32_t y = 0xffffffffu;
-            if (lane < 16) {
-                if (ai && (uint32_t)lane >= ai && (uint32_t)lane < endb) y = lane;
-            } else {
-                const uint32_t t = 16u * F1 + (lane - 16);
-                if (t < endb && (F1 > 0u || ai == 0u)) y = t;
+            // first partial vector: bytes [ai, min(16, endb)) by lanes 0-15; last one: [16*F1, endb) by lanes 16-31
+            const uint32_t y = lane < 16 ? (uint32_t)lane : 16u * F1 + (uint32_t)(lane - 16);
+            const bool okb = act && y < endb && (lane < 16 ? (ai != 0u && y >= ai) : (F1 > 0u || ai == 0u));
+            const uint32_t bsrc = (y < hend ? hbi : sb) + y;
+            if (okb) gdst[y] = (uint8_t)lds8(bsrc);
+        }
+        if (slow) {                                                                // records off the fast path
+#pragma unroll 1
+            for (uint32_t i = 0; i < nrec; ++i) {
+                const uint4 P = lds128(s_par + i * 16u);
+                if ((P.w & 3u) != 1u) continue;
+                const uint32_t kk = i >= tp ? 1u : 0u, pp = tile * tp + (i - kk * tp);
+                emit_generic(b, (int)kk, pp, b.cls[pp], P.x, lane);
             }
-            if (y != 0xffffffffu) gdst[y] = (uint8_t)(y < ai + Ji ? lds8(hsi + y) : lds8(srcb + y));
         }
         __syncwarp();
+        if (C3_STAGES == 1 && ntile < n_tiles) issue(nxt, 0u);
         cur = nxt;
     }
 }

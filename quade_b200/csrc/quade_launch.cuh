@@ -5,7 +5,7 @@ namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------------------
-static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 2;
+static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 3;
 void set_compact_variant(int v) { g_compact_variant = v; }
 
 static void init_launch_config()
