@@ -109,13 +109,14 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
     // sizes
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
-    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4];
+    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4];
+    uint32_t sfx_slot[4] = {0, 0, 0, 0};
     const size_t o_zero = take(0);
     const size_t o_state = take(sizeof(BatchState));
     const size_t o_counters = take((size_t)nb * 8);
     for (int s = 0; s < ns; ++s) {
         o_sf[s] = take(frame_tiles * 8);
-        o_sv[s] = take(val_tiles * 8);
+        o_sv[s] = take((val_tiles > frame_tiles ? val_tiles : frame_tiles) * 8);
     }
     const size_t zero_end = off;
     for (int s = 0; s < ns; ++s) {
@@ -128,6 +129,16 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         o_rec[s] = take(cap_rec * 16);
         o_vnlen[s] = take(cap_rec * 4);
         o_vrec[s] = take(cap_rec * 4);
+        o_vend[s] = take(cap_rec * 4);
+        o_dig[s] = o_sfx[s] = 0;
+        if (s >= 2) {   // index reads: digest + raw span bytes (k_frame2)
+            const uint32_t wi = (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]);
+            const uint32_t wm = (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]);
+            sfx_slot[s] = (((wi + 3u) & ~3u) + ((wm + 3u) & ~3u) + 15u) & ~15u;
+            if (sfx_slot[s] < 16u) sfx_slot[s] = 16u;
+            o_dig[s] = take(cap_rec * 16);
+            o_sfx[s] = take(cap_rec * sfx_slot[s] + 64);
+        }
     }
     const size_t o_cls = take(cap_pairs * 4), o_len1 = take(cap_pairs * 4), o_len2 = take(cap_pairs * 4);
     const size_t o_out1 = take(cap_pairs * 4), o_out2 = take(cap_pairs * 4);
@@ -173,6 +184,12 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         st.rec = reinterpret_cast<uint4 *>(A + o_rec[s]);
         st.vnlen = reinterpret_cast<uint32_t *>(A + o_vnlen[s]);
         st.vrec = reinterpret_cast<uint32_t *>(A + o_vrec[s]);
+        st.vend = reinterpret_cast<uint32_t *>(A + o_vend[s]);
+        st.dig = s >= 2 ? reinterpret_cast<uint4 *>(A + o_dig[s]) : nullptr;
+        st.sfx = s >= 2 ? A + o_sfx[s] : nullptr;
+        st.sfx_slot = sfx_slot[s];
+        st.wi = s >= 2 ? (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]) : 0u;
+        st.wm = s >= 2 ? (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]) : 0u;
         st.status_frame = reinterpret_cast<unsigned long long *>(A + o_sf[s]);
         st.status_validate = reinterpret_cast<unsigned long long *>(A + o_sv[s]);
     }
@@ -263,6 +280,7 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->cap_blocks = (uint32_t)((c->cap_pairs + ppb - 1) / ppb);
     c->cumulative.assign(c->n_bins, 0);
     if (const char *v = getenv("QUADE_COMPACT")) set_compact_variant(atoi(v));
+    if (const char *v = getenv("QUADE_FRAME")) set_frame_variant(atoi(v));
     int rc = QUADE_OK;
     if (cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking) != cudaSuccess ||

@@ -48,6 +48,11 @@ struct StreamDev {
     uint32_t *e1, *e3, *noff, *nlen;
     uint4 *rec;
     uint32_t *vnlen, *vrec;
+    // k_frame2 (fused frame + validate + index digest)
+    uint32_t *vend;                      // position just after the v-th valid record's last line
+    uint4 *dig;                          // index streams: {key lo, key hi, N mask, in | mn << 8 | min qual byte << 16 | bad << 24}
+    uint8_t *sfx;                        // index streams: raw index bytes at [0, in), raw molecular bytes at [wi, wi + mn)
+    uint32_t sfx_slot, wi, wm;           // slot bytes (multiple of 16), widths of the index / molecular spans
     unsigned long long *status_frame;    // decoupled look-back words, one per 16 KiB tile
     unsigned long long *status_validate; // one per 1024-record tile
 };
@@ -106,6 +111,11 @@ __host__ __device__ inline uint32_t key_slot(uint64_t h, uint32_t disp, uint32_t
 
 // launchers (quade_kernels.cu).  All enqueue on `s`; sizes unknown to the host are read from BatchState.
 void launch_frame(const BatchDev &b, cudaStream_t s);
+void launch_frame2(const BatchDev &b, cudaStream_t s);
+void launch_pairing2(const BatchDev &b, cudaStream_t s);
+void launch_classify2(const BatchDev &b, cudaStream_t s);
+void set_frame_variant(int v);
+int frame_variant();     // 2 = fused TMA-staged k_frame2 + digest classify (default), 1 = k_frame/k_validate/k_classify
 void launch_validate(const BatchDev &b, cudaStream_t s);
 void launch_pairing(const BatchDev &b, cudaStream_t s);
 void launch_classify(const BatchDev &b, cudaStream_t s);

@@ -12,6 +12,7 @@
 // All of it is byte / integer work bound by HBM bandwidth: 128-bit coalesced loads, warp ballots and shuffles,
 // shared-memory staging; no tensor cores.
 #include "quade_dev.h"
+#include "quade_ptx.cuh"
 
 namespace quade {
 namespace {
@@ -311,6 +312,7 @@ __global__ void __launch_bounds__(FT) k_frame(const __grid_constant__ BatchDev b
 } // namespace quade
 
 #include "quade_kernels2.cuh"
+#include "quade_frame2.cuh"
 #include "quade_kernels3.cuh"
 #include "quade_compact.cuh"
 #include "quade_compact3.cuh"

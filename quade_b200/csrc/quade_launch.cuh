@@ -7,6 +7,9 @@ namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 3;
 void set_compact_variant(int v) { g_compact_variant = v; }
+static int g_frame_variant = 1, g_occ_frame2 = 0;
+void set_frame_variant(int v) { g_frame_variant = v; }
+int frame_variant() { return g_frame_variant; }
 
 static void init_launch_config()
 {
@@ -19,6 +22,9 @@ static void init_launch_config()
     cudaFuncSetAttribute(k_compact, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCompactSmem);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact, k_compact, KT, kCompactSmem);
     if (g_occ_frame < 1) g_occ_frame = 1;
+    cudaFuncSetAttribute(k_frame2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F2_SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_frame2, k_frame2, F2T, F2_SMEM);
+    if (g_occ_frame2 < 1) g_occ_frame2 = 1;
     if (g_occ_validate < 1) g_occ_validate = 1;
     if (g_occ_compact < 1) g_occ_compact = 1;
     cudaFuncSetAttribute(k_compact3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM);
@@ -34,6 +40,32 @@ void launch_frame(const BatchDev &b, cudaStream_t s)
     uint32_t grid = (uint32_t)(g_sms * g_occ_frame);
     if (grid > total) grid = total;
     k_frame<<<grid, FT, 0, s>>>(b, total);
+}
+
+void launch_frame2(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    const uint32_t total = b.frame_tile_start[b.n_streams];
+    if (!total) return;
+    uint32_t grid = (uint32_t)(g_sms * g_occ_frame2);
+    if (grid > total) grid = total;
+    k_frame2<<<grid, F2T, F2_SMEM, s>>>(b, total);
+}
+
+void launch_pairing2(const BatchDev &b, cudaStream_t s) { k_pairing2<<<1, 32, 0, s>>>(b); }
+
+void launch_classify2(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    bool in_smem;
+    size_t sm = classify_smem_bytes(b, &in_smem);
+    cudaFuncSetAttribute(k_classify2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_classify2, C2T, sm);
+    if (occ < 1) occ = 1;
+    uint32_t grid = (uint32_t)(g_sms * occ);
+    if (grid > b.cap_blocks) grid = b.cap_blocks;
+    k_classify2<<<grid, C2T, sm, s>>>(b, in_smem ? 1 : 0);
 }
 
 void launch_validate(const BatchDev &b, cudaStream_t s)
