@@ -109,7 +109,7 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
     // sizes
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
-    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4];
+    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4], o_rec_t[4], o_vnlen_t[4], o_vend_t[4], o_dig_t[4], o_sfx_t[4];
     uint32_t sfx_slot[4] = {0, 0, 0, 0};
     const size_t o_zero = take(0);
     const size_t o_state = take(sizeof(BatchState));
@@ -130,6 +130,12 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         o_vnlen[s] = take(cap_rec * 4);
         o_vrec[s] = take(cap_rec * 4);
         o_vend[s] = take(cap_rec * 4);
+        o_vend_t[s] = take(cap_rec * 4);
+        o_rec_t[s] = o_vnlen_t[s] = o_dig_t[s] = o_sfx_t[s] = 0;
+        if (s < 2) {
+            o_rec_t[s] = take(cap_rec * 16);
+            o_vnlen_t[s] = take(cap_rec * 4);
+        }
         o_dig[s] = o_sfx[s] = 0;
         if (s >= 2) {   // index reads: digest + raw span bytes (k_frame2)
             const uint32_t wi = (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]);
@@ -138,6 +144,8 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
             if (sfx_slot[s] < 16u) sfx_slot[s] = 16u;
             o_dig[s] = take(cap_rec * 16);
             o_sfx[s] = take(cap_rec * sfx_slot[s] + 64);
+            o_dig_t[s] = take(cap_rec * 16);
+            o_sfx_t[s] = take(cap_rec * sfx_slot[s] + 64);
         }
     }
     const size_t o_cls = take(cap_pairs * 4), o_len1 = take(cap_pairs * 4), o_len2 = take(cap_pairs * 4);
@@ -187,6 +195,11 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         st.vend = reinterpret_cast<uint32_t *>(A + o_vend[s]);
         st.dig = s >= 2 ? reinterpret_cast<uint4 *>(A + o_dig[s]) : nullptr;
         st.sfx = s >= 2 ? A + o_sfx[s] : nullptr;
+        st.vend_t = reinterpret_cast<uint32_t *>(A + o_vend_t[s]);
+        st.rec_t = s < 2 ? reinterpret_cast<uint4 *>(A + o_rec_t[s]) : nullptr;
+        st.vnlen_t = s < 2 ? reinterpret_cast<uint32_t *>(A + o_vnlen_t[s]) : nullptr;
+        st.dig_t = s >= 2 ? reinterpret_cast<uint4 *>(A + o_dig_t[s]) : nullptr;
+        st.sfx_t = s >= 2 ? A + o_sfx_t[s] : nullptr;
         st.sfx_slot = sfx_slot[s];
         st.wi = s >= 2 ? (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]) : 0u;
         st.wm = s >= 2 ? (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]) : 0u;

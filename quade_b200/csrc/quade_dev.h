@@ -27,6 +27,7 @@ constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
 struct BatchState {
     uint32_t n_lines[kMaxStreams];
     uint32_t n_valid[kMaxStreams];
+    uint32_t n_invalid[kMaxStreams];   // k_frame2: complete records with len(seq) != len(qual)
     uint32_t first_blank[kMaxStreams]; // lowest record index with an empty name token, or 0xffffffff
     uint32_t n_pairs;
     uint32_t n_blocks;
@@ -52,6 +53,9 @@ struct StreamDev {
     uint32_t *vend;                      // position just after the v-th valid record's last line
     uint4 *dig;                          // index streams: {key lo, key hi, N mask, in | mn << 8 | min qual byte << 16 | bad << 24}
     uint8_t *sfx;                        // index streams: raw index bytes at [0, in), raw molecular bytes at [wi, wi + mn)
+    uint4 *rec_t, *dig_t;                // scratch of k_fix_compact (rare path: files with invalid records)
+    uint32_t *vnlen_t, *vend_t;
+    uint8_t *sfx_t;
     uint32_t sfx_slot, wi, wm;           // slot bytes (multiple of 16), widths of the index / molecular spans
     unsigned long long *status_frame;    // decoupled look-back words, one per 16 KiB tile
     unsigned long long *status_validate; // one per 1024-record tile
@@ -112,6 +116,7 @@ __host__ __device__ inline uint32_t key_slot(uint64_t h, uint32_t disp, uint32_t
 // launchers (quade_kernels.cu).  All enqueue on `s`; sizes unknown to the host are read from BatchState.
 void launch_frame(const BatchDev &b, cudaStream_t s);
 void launch_frame2(const BatchDev &b, cudaStream_t s);
+void launch_fix(const BatchDev &b, cudaStream_t s);
 void launch_pairing2(const BatchDev &b, cudaStream_t s);
 void launch_classify2(const BatchDev &b, cudaStream_t s);
 void set_frame_variant(int v);

@@ -392,56 +392,109 @@ __global__ void __launch_bounds__(F2T) k_frame2(const __grid_constant__ BatchDev
             }
             return f2_parse(T, hs, s_pos, li, npos);
         };
-        // 4. + 5. one thread per record start; ordinal among the valid records; outputs
-        const uint32_t ngroups = (nslot + F2T - 1u) / F2T;
-        uint32_t vtotal = 0;
-        F2Rec R;
-        R.complete = R.valid = false;
-        for (uint32_t g = 0; g < ngroups; ++g) {             // pass A: count the valid records of the tile
-            const uint32_t slot = g * F2T + tid;
-            R.complete = R.valid = false;
-            if (slot < nslot) R = parse_slot(slot);
-            vtotal += __syncthreads_count(R.valid);
-        }
-        if (warp == 0) {
-            const uint32_t vb = lookback(st.status_validate, (int)lt, vtotal, lane);
-            if (lane == 0) {
-                s_misc[9] = vb;
-                if ((u64)tbase + F2_TILE > (u64)n) S->n_valid[s] = vb + vtotal;
-            }
-        }
-        __syncthreads();
-        uint32_t vrun = s_misc[9];
-        for (uint32_t g = 0; g < ngroups; ++g) {             // pass B: write (re-parse only when there are several groups)
-            const uint32_t slot = g * F2T + tid;
-            if (ngroups > 1u) {
-                R.complete = R.valid = false;
-                if (slot < nslot) R = parse_slot(slot);
-            }
-            uint32_t gtotal;
-            const uint32_t ex = block_scan256(R.valid ? 1u : 0u, s_misc, &gtotal);
+        // 4. one thread per record start, outputs at the RAW record index j.  Records with len(seq) != len(qual)
+        //    are flagged (bit 31) and counted; they are rare, and only when a file has some does k_fix_compact
+        //    squeeze them out afterwards (pairing ordinal = rank among the valid records, FastqReader.py:48-50).
+        for (uint32_t slot = tid; slot < nslot; slot += F2T) {
+            const F2Rec R = parse_slot(slot);
+            if (!R.complete) continue;
             const uint32_t j = rbase + slot;
-            if (R.complete && R.nlen == 0u) atomicMax(&S->first_blank[s], ~j);   // keeps the LOWEST blank record index
-            if (R.valid) {
-                const uint32_t v = vrun + ex;
-                if (v < st.cap_rec) {
-                    st.vrec[v] = j;
-                    st.vend[v] = R.end;
-                    if (s < 2) {
-                        st.rec[v] = make_uint4(R.name_off, R.seq_off, R.qual_off, R.seq_len);
-                        st.vnlen[v] = R.nlen;
-                    } else {
-                        f2_digest(b, st, s, T, R, v);
-                    }
-                } else {
-                    S->err_capacity = 1u;
-                }
+            if (j >= st.cap_rec) { S->err_capacity = 1u; continue; }
+            if (R.nlen == 0u) atomicMax(&S->first_blank[s], ~j);               // keeps the LOWEST blank record index
+            const uint32_t inv = R.valid ? 0u : 0x80000000u;
+            if (inv) atomicAdd(&S->n_invalid[s], 1u);
+            st.vend[j] = R.end;
+            if (s < 2) {
+                st.rec[j] = make_uint4(R.name_off, R.seq_off, R.qual_off, R.seq_len | inv);
+                st.vnlen[j] = R.nlen;
+            } else if (inv) {
+                st.dig[j] = make_uint4(0u, 0u, 0u, inv);
+            } else {
+                f2_digest(b, st, s, T, R, j);
             }
-            vrun += gtotal;
-            __syncthreads();
         }
         tile = s_misc[10 + ((it + 1u) & 1u)];
         __syncthreads();                                      // bitmap, starts and the stage are reused
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// K2': rare path.  A file that holds records with len(seq) != len(qual) gets them squeezed out: stable
+// compaction of its per-record arrays (tiles of 1024 records, decoupled look-back) into scratch arrays, then a
+// copy back.  Files without such records (the normal case) return at once: raw record index = pairing ordinal.
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool f2_is_invalid(const StreamDev &st, int s, uint32_t j)
+{
+    return ((s < 2 ? st.rec[j].w : st.dig[j].w) >> 31) != 0u;
+}
+
+__global__ void __launch_bounds__(256) k_fix_compact(const __grid_constant__ BatchDev b)
+{
+    __shared__ uint32_t s_warp[9];
+    __shared__ uint32_t s_tile, s_base;
+    const int s = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    BatchState *S = b.state;
+    if (S->n_invalid[s] == 0u) return;
+    const StreamDev &st = b.st[s];
+    const uint32_t n_rec = min(S->n_lines[s] >> 2, st.cap_rec);
+    const uint32_t n_tiles = (n_rec + kValidateTile - 1) / kValidateTile, sv = st.sfx_slot >> 4;
+    for (;;) {
+        if (tid == 0) s_tile = atomicAdd(&S->ticket_validate[s], 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= n_tiles) return;
+        const uint32_t j0 = tile * kValidateTile + (uint32_t)tid * 4u;
+        uint32_t vmask = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (j0 + i < n_rec && !f2_is_invalid(st, s, j0 + i)) vmask |= 1u << i;
+        uint32_t total;
+        const uint32_t excl = block_scan256((uint32_t)__popc(vmask), s_warp, &total);
+        if (warp == 0) {
+            const uint32_t base = lookback(st.status_validate, (int)tile, total, lane);
+            if (lane == 0) s_base = base;
+        }
+        __syncthreads();
+        uint32_t v = s_base + excl;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (!(vmask & (1u << i))) continue;
+            const uint32_t j = j0 + i;
+            st.vrec[v] = j;
+            st.vend_t[v] = st.vend[j];
+            if (s < 2) {
+                st.rec_t[v] = st.rec[j];
+                st.vnlen_t[v] = st.vnlen[j];
+            } else {
+                st.dig_t[v] = st.dig[j];
+                const uint4 *src = reinterpret_cast<const uint4 *>(st.sfx + (size_t)j * st.sfx_slot);
+                uint4 *dst = reinterpret_cast<uint4 *>(st.sfx_t + (size_t)v * st.sfx_slot);
+                for (uint32_t q = 0; q < sv; ++q) dst[q] = src[q];
+            }
+            ++v;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(256) k_fix_copyback(const __grid_constant__ BatchDev b)
+{
+    const int s = blockIdx.y;
+    const BatchState *S = b.state;
+    if (S->n_invalid[s] == 0u) return;
+    const StreamDev &st = b.st[s];
+    const uint32_t n_rec = min(S->n_lines[s] >> 2, st.cap_rec), nv = n_rec - min(n_rec, S->n_invalid[s]), sv = st.sfx_slot >> 4;
+    for (uint32_t v = blockIdx.x * 256u + threadIdx.x; v < nv; v += gridDim.x * 256u) {
+        st.vend[v] = st.vend_t[v];
+        if (s < 2) {
+            st.rec[v] = st.rec_t[v];
+            st.vnlen[v] = st.vnlen_t[v];
+        } else {
+            st.dig[v] = st.dig_t[v];
+            const uint4 *src = reinterpret_cast<const uint4 *>(st.sfx_t + (size_t)v * st.sfx_slot);
+            uint4 *dst = reinterpret_cast<uint4 *>(st.sfx + (size_t)v * st.sfx_slot);
+            for (uint32_t q = 0; q < sv; ++q) dst[q] = src[q];
+        }
     }
 }
 
@@ -453,7 +506,11 @@ __global__ void k_pairing2(const __grid_constant__ BatchDev b)
     if (threadIdx.x != 0) return;
     BatchState *S = b.state;
     uint32_t np = 0xffffffffu;
-    for (int s = 0; s < b.n_streams; ++s) np = min(np, S->n_valid[s]);
+    for (int s = 0; s < b.n_streams; ++s) {
+        const uint32_t n_rec = min(S->n_lines[s] >> 2, b.st[s].cap_rec);
+        S->n_valid[s] = n_rec - min(n_rec, S->n_invalid[s]);
+        np = min(np, S->n_valid[s]);
+    }
     if (np > b.cap_pairs) {
         S->err_capacity = 1u;
         np = 0;
@@ -463,16 +520,18 @@ __global__ void k_pairing2(const __grid_constant__ BatchDev b)
     while (S->n_valid[sx] != np && sx + 1 < b.n_streams) ++sx;   // first file (in pull order) that runs dry
     for (int s = 0; s < b.n_streams && !S->err_capacity; ++s) {
         const StreamDev &st = b.st[s];
+        const bool sq = S->n_invalid[s] != 0u;                  // squeezed: vrec[v] = raw index, else v itself
+        auto vrec = [&](uint32_t v) { return sq ? st.vrec[v] : v; };
         if (np > 0) {
             S->consumed[s] = st.vend[np - 1];
-            S->n_skipped[s] = st.vrec[np - 1] + 1u - np;
+            S->n_skipped[s] = vrec(np - 1) + 1u - np;
         }
         if (S->first_blank[s]) {
             const uint32_t jb = ~S->first_blank[s];
             bool parsed;
-            if (s < sx) parsed = jb <= st.vrec[np];             // pulled once more in the failing iteration
+            if (s < sx) parsed = jb <= vrec(np);             // pulled once more in the failing iteration
             else if (s == sx) parsed = true;                     // parsed to the end looking for a valid record
-            else parsed = np > 0 && jb <= st.vrec[np - 1];
+            else parsed = np > 0 && jb <= vrec(np - 1);
             if (parsed) S->err_blank = 1u;
         }
     }

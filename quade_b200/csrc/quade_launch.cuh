@@ -52,6 +52,14 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
     k_frame2<<<grid, F2T, F2_SMEM, s>>>(b, total);
 }
 
+void launch_fix(const BatchDev &b, cudaStream_t s)
+{
+    init_launch_config();
+    const uint32_t gx = (uint32_t)max(1, g_sms * 4 / b.n_streams);
+    k_fix_compact<<<dim3(gx, b.n_streams), 256, 0, s>>>(b);
+    k_fix_copyback<<<dim3(gx, b.n_streams), 256, 0, s>>>(b);
+}
+
 void launch_pairing2(const BatchDev &b, cudaStream_t s) { k_pairing2<<<1, 32, 0, s>>>(b); }
 
 void launch_classify2(const BatchDev &b, cudaStream_t s)
