@@ -27,8 +27,9 @@ constexpr int F2_WORDS = F2_WIN / 64;          // 64-bit bitmap words (288)
 constexpr int F2_PCAP = 4096;                  // line ends of a window kept as a dense list (else: bitmap search)
 constexpr uint32_t F2_NONE = 0xffffffffu;
 
-constexpr int F2_OFF_DATA = 0;                                   // [2][F2_WIN + 16]
-constexpr int F2_OFF_BM = 2 * (F2_WIN + 16);                     // u64[F2_WORDS] newlines
+constexpr int F2_OFF_DATA = 0;                                   // [F2_STAGES][F2_WIN + 16]
+constexpr int F2_STAGES = 1;                   // 1: ticket taken just in time, more CTAs per SM hide the copy latency
+constexpr int F2_OFF_BM = F2_STAGES * (F2_WIN + 16);             // u64[F2_WORDS] newlines
 constexpr int F2_OFF_BC = F2_OFF_BM + F2_WORDS * 8;              // u64[F2_WORDS] bytes <= 0x20 (blank candidates)
 constexpr int F2_OFF_POS = F2_OFF_BC + F2_WORDS * 8;             // u16[F2_PCAP] window offsets of the line ends
 constexpr int F2_OFF_MISC = F2_OFF_POS + F2_PCAP * 2;
@@ -40,7 +41,7 @@ struct F2Tile {
     const u64 *bm;          // newline bitmap, bit i = byte tbase + i (i < win)
     const u64 *bc;          // bitmap of the bytes <= 0x20: every blank is in there
     uint32_t tbase, n, win; // win: staged bytes that exist (<= F2_WIN)
-    bool vnl;               // the file ends without '\n' and this is its last batch: position n counts as one
+    bool last;              // last batch of the file: if it ends without '\n', position n counts as a line end
 };
 
 __device__ __forceinline__ uint32_t f2_byte(const F2Tile &t, uint32_t pos)
@@ -66,7 +67,7 @@ __device__ __forceinline__ uint32_t f2_next_nl(const F2Tile &t, uint32_t from)
     }
     for (u64 p = from; p < t.n; ++p)
         if (t.data[p] == '\n') return (uint32_t)p;
-    return (t.vnl && from <= t.n) ? t.n : F2_NONE;
+    return (t.last && t.n > 0u && from <= t.n && t.data[t.n - 1u] != '\n') ? t.n : F2_NONE;
 }
 
 // is the byte at global position pos <= 0x20 ?
@@ -231,7 +232,7 @@ __device__ __forceinline__ void f2_digest(const BatchDev &b, const StreamDev &st
     st.dig[v] = make_uint4((uint32_t)key, (uint32_t)(key >> 32), nm, in | mn << 8 | minq << 16 | bad << 24);
 }
 
-__global__ void __launch_bounds__(F2T) k_frame2(const __grid_constant__ BatchDev b, uint32_t total_tiles)
+__global__ void __launch_bounds__(F2T, 6) k_frame2(const __grid_constant__ BatchDev b, uint32_t total_tiles)
 {
     extern __shared__ __align__(128) uint8_t f2_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -273,8 +274,8 @@ __global__ void __launch_bounds__(F2T) k_frame2(const __grid_constant__ BatchDev
     uint32_t tile = s_misc[10], phase_bits = 0;
 
     for (uint32_t it = 0; tile < total_tiles; ++it) {
-        const uint32_t stage = it & 1u;
-        if (tid == 0) {                                      // next ticket, its copy flies while this tile is parsed
+        const uint32_t stage = F2_STAGES == 2 ? (it & 1u) : 0u;
+        if (F2_STAGES == 2 && tid == 0) {                    // next ticket, its copy flies while this tile is parsed
             const uint32_t tn = atomicAdd(&S->ticket_frame, 1u);
             s_misc[10 + ((it + 1u) & 1u)] = tn;
             if (tn < total_tiles) issue(tn, stage ^ 1u);
@@ -298,7 +299,7 @@ __global__ void __launch_bounds__(F2T) k_frame2(const __grid_constant__ BatchDev
         T.tbase = tbase;
         T.n = n;
         T.win = n > tbase ? min((uint32_t)F2_WIN, n - tbase) : 0u;
-        T.vnl = ((b.last >> s) & 1) && n > 0u && f2_byte(T, n - 1u) != '\n';
+        T.last = ((b.last >> s) & 1) != 0;
 
         // 1. newline / candidate bitmaps of the window: 64 bytes per thread (+ the halo by warp 0)
         u64 mine = 0, halo = 0;
@@ -312,7 +313,8 @@ __global__ void __launch_bounds__(F2T) k_frame2(const __grid_constant__ BatchDev
                     cd &= (1ull << (T.win - c0)) - 1ull;
                 }
             }
-            if (T.vnl && n - tbase >= c0 && n - tbase < c0 + 64u) m |= 1ull << (n - tbase - c0);
+            if (T.last && n > 0u && n - tbase >= c0 && n - tbase < c0 + 64u && f2_byte(T, n - 1u) != '\n')
+                m |= 1ull << (n - tbase - c0);                // the file's last line has no '\n'
             s_bm[c] = m;
             s_bc[c] = cd;
             if (c < F2T) mine = m; else halo = m;
@@ -413,8 +415,21 @@ __global__ void __launch_bounds__(F2T) k_frame2(const __grid_constant__ BatchDev
                 f2_digest(b, st, s, T, R, j);
             }
         }
-        tile = s_misc[10 + ((it + 1u) & 1u)];
-        __syncthreads();                                      // bitmap, starts and the stage are reused
+        if (F2_STAGES == 2) {
+            tile = s_misc[10 + ((it + 1u) & 1u)];
+            __syncthreads();                                  // bitmap, list and the stage are reused
+        } else {
+            // A ticket held while another tile is parsed would make every successor spin in its look-back for a
+            // whole tile time: take it just in time; the other CTAs of the SM cover the copy latency.
+            __syncthreads();
+            if (tid == 0) {
+                const uint32_t tn = atomicAdd(&S->ticket_frame, 1u);
+                s_misc[10] = tn;
+                if (tn < total_tiles) issue(tn, 0u);
+            }
+            __syncthreads();
+            tile = s_misc[10];
+        }
     }
 }
 

@@ -7,7 +7,7 @@ namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 3;
 void set_compact_variant(int v) { g_compact_variant = v; }
-static int g_frame_variant = 1, g_occ_frame2 = 0;
+static int g_frame_variant = 2, g_occ_frame2 = 0;
 void set_frame_variant(int v) { g_frame_variant = v; }
 int frame_variant() { return g_frame_variant; }
 
