@@ -105,7 +105,7 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
 {
     const int ns = c->n_streams, nb = c->n_bins;
     const size_t cap_rec = c->cap_rec, cap_pairs = c->cap_pairs;
-    const size_t frame_tiles = c->cap_bytes / kFrameTile + 2, val_tiles = cap_rec / kValidateTile + 2;
+    const size_t frame_tiles = c->cap_bytes / kFrameTileMin + 2, val_tiles = cap_rec / kValidateTile + 2;
     // sizes
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };

@@ -131,7 +131,8 @@ void set_compact_variant(int v);   // 3 = TMA-staged k_compact3 (default), 2 = c
 int kernel_launch_count(int stage);
 size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
 
-constexpr int kFrameTile = 16384;   // bytes per frame tile
+constexpr int kFrameTile = 16384;   // bytes per frame tile (k_frame, k_frame2, k_frame3)
+constexpr int kFrameTileMin = 8192; // smallest tile of any frame kernel (sizes the look-back status arrays)
 constexpr int kFrameHalo = 256;
 constexpr int kValidateTile = 1024; // records per validate tile
 

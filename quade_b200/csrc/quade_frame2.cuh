@@ -40,7 +40,8 @@ struct F2Tile {
     uint32_t sdata;         // shared address of byte `tbase`
     const u64 *bm;          // newline bitmap, bit i = byte tbase + i (i < win)
     const u64 *bc;          // bitmap of the bytes <= 0x20: every blank is in there
-    uint32_t tbase, n, win; // win: staged bytes that exist (<= F2_WIN)
+    uint32_t tbase, n, win; // win: staged bytes that exist (<= cap)
+    uint32_t cap;           // window capacity in bytes (multiple of 64)
     bool last;              // last batch of the file: if it ends without '\n', position n counts as a line end
 };
 
@@ -55,15 +56,15 @@ __device__ __forceinline__ uint32_t f2_byte(const F2Tile &t, uint32_t pos)
 __device__ __forceinline__ uint32_t f2_next_nl(const F2Tile &t, uint32_t from)
 {
     uint32_t q = from - t.tbase;
-    if (q < (uint32_t)F2_WIN) {
+    if (q < t.cap) {
         uint32_t w = q >> 6;
         u64 m = t.bm[w] & (~0ull << (q & 63u));
         for (;;) {
             if (m) return t.tbase + w * 64u + (uint32_t)__ffsll((long long)m) - 1u;
-            if (++w >= (uint32_t)F2_WORDS) break;
+            if (++w >= (t.cap >> 6)) break;
             m = t.bm[w];
         }
-        from = t.tbase + (uint32_t)F2_WIN;
+        from = t.tbase + t.cap;
     }
     for (u64 p = from; p < t.n; ++p)
         if (t.data[p] == '\n') return (uint32_t)p;
@@ -80,7 +81,7 @@ __device__ __forceinline__ bool f2_cand(const F2Tile &t, uint32_t pos)
 __device__ __forceinline__ uint32_t f2_next_cand(const F2Tile &t, uint32_t from, uint32_t e)
 {
     uint32_t q = from - t.tbase;
-    if (q < (uint32_t)F2_WIN) {
+    if (q < t.cap) {
         uint32_t w = q >> 6;
         u64 m = t.bc[w] & (~0ull << (q & 63u));
         for (;;) {
@@ -88,10 +89,10 @@ __device__ __forceinline__ uint32_t f2_next_cand(const F2Tile &t, uint32_t from,
                 const uint32_t p = t.tbase + w * 64u + (uint32_t)__ffsll((long long)m) - 1u;
                 return p < e ? p : e;
             }
-            if (++w >= (uint32_t)F2_WORDS || t.tbase + w * 64u >= e) break;
+            if (++w >= (t.cap >> 6) || t.tbase + w * 64u >= e) break;
             m = t.bc[w];
         }
-        from = t.tbase + (uint32_t)F2_WIN;
+        from = t.tbase + t.cap;
     }
     for (u64 p = from; p < e; ++p)
         if (t.data[p] <= 0x20u) return (uint32_t)p;
@@ -297,6 +298,7 @@ __global__ void __launch_bounds__(F2T, 6) k_frame2(const __grid_constant__ Batch
         T.bm = s_bm;
         T.bc = s_bc;
         T.tbase = tbase;
+        T.cap = (uint32_t)F2_WIN;
         T.n = n;
         T.win = n > tbase ? min((uint32_t)F2_WIN, n - tbase) : 0u;
         T.last = ((b.last >> s) & 1) != 0;

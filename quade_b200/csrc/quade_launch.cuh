@@ -7,7 +7,7 @@ namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 3;
 void set_compact_variant(int v) { g_compact_variant = v; }
-static int g_frame_variant = 2, g_occ_frame2 = 0;
+static int g_frame_variant = 2, g_occ_frame2 = 0, g_occ_frame3 = 0;   // 3 = k_frame3 (opt-in for now)
 void set_frame_variant(int v) { g_frame_variant = v; }
 int frame_variant() { return g_frame_variant; }
 
@@ -25,6 +25,9 @@ static void init_launch_config()
     cudaFuncSetAttribute(k_frame2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F2_SMEM);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_frame2, k_frame2, F2T, F2_SMEM);
     if (g_occ_frame2 < 1) g_occ_frame2 = 1;
+    cudaFuncSetAttribute(k_frame3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_frame3, k_frame3, F3T, F3_SMEM);
+    if (g_occ_frame3 < 1) g_occ_frame3 = 1;
     if (g_occ_validate < 1) g_occ_validate = 1;
     if (g_occ_compact < 1) g_occ_compact = 1;
     cudaFuncSetAttribute(k_compact3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM);
@@ -47,6 +50,37 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
     init_launch_config();
     const uint32_t total = b.frame_tile_start[b.n_streams];
     if (!total) return;
+    if (g_frame_variant == 4 || g_frame_variant == 5) {      // 4: 16 KiB tiles, 5: 8 KiB tiles
+        static int backoff = -1, occ16 = 0, occ8 = 0;
+        if (backoff < 0) {
+            const char *v = getenv("QUADE_F3_BACKOFF");
+            backoff = v ? atoi(v) : 256;
+            cudaFuncSetAttribute(k_frame4<16384>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F4<16384>::SMEM);
+            cudaFuncSetAttribute(k_frame4<8192>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F4<8192>::SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ16, k_frame4<16384>, F4<16384>::NT, F4<16384>::SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ8, k_frame4<8192>, F4<8192>::NT, F4<8192>::SMEM);
+            if (const char *o = getenv("QUADE_F4_OCC")) occ16 = occ8 = atoi(o);
+        }
+        const uint32_t tb = g_frame_variant == 4 ? 16384u : 8192u;
+        uint32_t tiles = 0;
+        for (int i = 0; i < b.n_streams; ++i) tiles += b.st[i].n ? b.st[i].n / tb + 1u : 0u;
+        uint32_t g4 = (uint32_t)(g_sms * max(1, g_frame_variant == 4 ? occ16 : occ8));
+        if (g4 > tiles) g4 = tiles;
+        if (g_frame_variant == 4) k_frame4<16384><<<g4, F4<16384>::NT, F4<16384>::SMEM, s>>>(b, tiles, (uint32_t)backoff);
+        else k_frame4<8192><<<g4, F4<8192>::NT, F4<8192>::SMEM, s>>>(b, tiles, (uint32_t)backoff);
+        return;
+    }
+    if (g_frame_variant == 3) {
+        uint32_t grid3 = (uint32_t)(g_sms * g_occ_frame3);
+        if (grid3 > total) grid3 = total;
+        static int backoff = -1;
+        if (backoff < 0) {
+            const char *v = getenv("QUADE_F3_BACKOFF");
+            backoff = v ? atoi(v) : 256;
+        }
+        k_frame3<<<grid3, F3T, F3_SMEM, s>>>(b, total, (uint32_t)backoff);
+        return;
+    }
     uint32_t grid = (uint32_t)(g_sms * g_occ_frame2);
     if (grid > total) grid = total;
     k_frame2<<<grid, F2T, F2_SMEM, s>>>(b, total);
@@ -145,6 +179,16 @@ void launch_compact(const BatchDev &b, cudaStream_t s)
     if (grid > need) grid = need;
     k_compact<<<grid, KT, kCompactSmem, s>>>(b);
 }
+
+#ifdef QUADE_F3_PROF
+extern "C" void quade_debug_f3_prof(unsigned long long *out)
+{
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_f3_prof, sizeof(unsigned long long) * 16);
+    unsigned long long z[16] = {0};
+    cudaMemcpyToSymbol(g_f3_prof, z, sizeof(z));
+}
+#endif
 
 int kernel_launch_count(int stage)
 {

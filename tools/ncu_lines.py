@@ -31,7 +31,7 @@ def sass_lines(lib, kernel):
             if m:
                 line = (os.path.basename(m.group(1)), int(m.group(2)))
                 continue
-            if cur_fn and kernel in cur_fn and re.match(r"\s*/\*[0-9a-f]{4}\*/", l):
+            if cur_fn and kernel in cur_fn and re.match(r"\s*/\*[0-9a-f]{4,}\*/", l):
                 out.append((line, l.split("*/", 1)[1].strip()))
         if out:
             break
@@ -45,6 +45,8 @@ def main():
     ap.add_argument("--top", type=int, default=30)
     ap.add_argument("--lib", default="quade_b200/libquade_b200.so")
     ap.add_argument("--launch", type=int, default=0, help="which matching launch in the report")
+    ap.add_argument("--by", default="inst", choices=["inst", "stall"])
+    ap.add_argument("--section", default=None, help="substring of the mangled name in the cubin (template instances)")
     a = ap.parse_args()
     txt = subprocess.run(["ncu", "-i", a.rep, "--page", "source", "--csv", "--kernel-name", "regex:" + a.kernel],
                          capture_output=True, text=True).stdout
@@ -60,7 +62,7 @@ def main():
     b = blocks[a.launch]
     h = b["hdr"]
     ie, ns, src = h.index("Instructions Executed"), h.index("# Samples"), h.index("Source")
-    lines = sass_lines(a.lib, a.kernel)
+    lines = sass_lines(a.lib, a.section or a.kernel)
     if len(lines) != len(b["rows"]):
         print("warning: %d SASS instructions in the library vs %d in the report" % (len(lines), len(b["rows"])))
     agg, tot_i, tot_s = {}, 0.0, 0.0
@@ -73,7 +75,7 @@ def main():
         tot_s += float(r[ns] or 0)
     print("%s: %d SASS instructions, %.0f warp-instructions executed, %.0f samples" % (b["name"], len(b["rows"]), tot_i, tot_s))
     srcs = {}
-    for (f, n), (i_, s_) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:a.top]:
+    for (f, n), (i_, s_) in sorted(agg.items(), key=lambda kv: -kv[1][0 if a.by == "inst" else 1])[:a.top]:
         if f not in srcs:
             p = os.path.join("quade_b200", "csrc", f)
             srcs[f] = open(p).read().splitlines() if os.path.exists(p) else []
