@@ -109,7 +109,7 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
     // sizes
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
-    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4], o_rec_t[4], o_vnlen_t[4], o_vend_t[4], o_dig_t[4], o_sfx_t[4];
+    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4], o_rec_t[4], o_vnlen_t[4], o_vend_t[4], o_dig_t[4], o_sfx_t[4], o_tt[4];
     uint32_t sfx_slot[4] = {0, 0, 0, 0};
     const size_t o_zero = take(0);
     const size_t o_state = take(sizeof(BatchState));
@@ -120,6 +120,7 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
     }
     const size_t zero_end = off;
     for (int s = 0; s < ns; ++s) {
+        o_tt[s] = take((c->cap_bytes / kFrameTile + 2) * 16);
         o_in[s] = take(c->cap_bytes + 256);
         o_nl[s] = take(cap_rec * 16);
         o_e1[s] = take(cap_rec * 4);
@@ -148,6 +149,8 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
             o_sfx_t[s] = take(cap_rec * sfx_slot[s] + 64);
         }
     }
+    const size_t redo_cap = (size_t)ns * (c->cap_bytes / kFrameTile + 2);
+    const size_t o_redo = take(redo_cap * 4);
     const size_t o_cls = take(cap_pairs * 4), o_len1 = take(cap_pairs * 4), o_len2 = take(cap_pairs * 4);
     const size_t o_out1 = take(cap_pairs * 4), o_out2 = take(cap_pairs * 4);
     const size_t o_suf = take(cap_pairs * c->suf_cap + 64);
@@ -205,7 +208,10 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         st.wm = s >= 2 ? (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]) : 0u;
         st.status_frame = reinterpret_cast<unsigned long long *>(A + o_sf[s]);
         st.status_validate = reinterpret_cast<unsigned long long *>(A + o_sv[s]);
+        st.tile_tab = reinterpret_cast<uint4 *>(A + o_tt[s]);
     }
+    d.redo_list = reinterpret_cast<uint32_t *>(A + o_redo);
+    d.redo_cap = (uint32_t)redo_cap;
     d.cls = reinterpret_cast<uint32_t *>(A + o_cls);
     d.len1 = reinterpret_cast<uint32_t *>(A + o_len1);
     d.len2 = reinterpret_cast<uint32_t *>(A + o_len2);

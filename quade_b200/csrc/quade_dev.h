@@ -38,6 +38,8 @@ struct BatchState {
     uint32_t ticket_frame;             // dynamic tile counters
     uint32_t ticket_validate[kMaxStreams];
     uint32_t compact_tp;               // pairs per k_compact3 tile, from the mean record size (k_pairing)
+    uint32_t scratch_cursor[kMaxStreams]; // k_frame6: records reserved in the per-stream scratch arrays
+    uint32_t n_redo, ticket_redo;      // k_frame6: tiles whose guessed record phase was wrong (malformed text)
     unsigned long long out_total[2];   // bytes of the R1 / R2 arenas
 };
 
@@ -59,6 +61,7 @@ struct StreamDev {
     uint32_t sfx_slot, wi, wm;           // slot bytes (multiple of 16), widths of the index / molecular spans
     unsigned long long *status_frame;    // decoupled look-back words, one per 16 KiB tile
     unsigned long long *status_validate; // one per 1024-record tile
+    uint4 *tile_tab;                     // k_frame6: per 16 KiB tile {line ends | k0, guess | ok, records, scratch base}
 };
 
 struct HashTable {
@@ -93,6 +96,8 @@ struct BatchDev {
     long long *counters;       // [n_bins] pair counts of this batch
     uint8_t *out[2];
     uint32_t frame_tile_start[kMaxStreams + 1];
+    uint32_t *redo_list;       // k_frame6: stream << 28 | tile of the tiles to parse again
+    uint32_t redo_cap;
 };
 
 // hash shared by the host builder and the device probe
@@ -116,6 +121,7 @@ __host__ __device__ inline uint32_t key_slot(uint64_t h, uint32_t disp, uint32_t
 // launchers (quade_kernels.cu).  All enqueue on `s`; sizes unknown to the host are read from BatchState.
 void launch_frame(const BatchDev &b, cudaStream_t s);
 void launch_frame2(const BatchDev &b, cudaStream_t s);
+int frame_launches();     // kernels launch_frame2 enqueues for the current variant
 void launch_fix(const BatchDev &b, cudaStream_t s);
 void launch_pairing2(const BatchDev &b, cudaStream_t s);
 void launch_classify2(const BatchDev &b, cudaStream_t s);

@@ -52,6 +52,9 @@ __device__ __forceinline__ uint32_t lookback_wide(u64 *status, int tile, uint32_
         if (lane == 0) st_status(status, ST_INC | total);
         return 0;
     }
+#ifdef QUADE_F3_PROF
+    if (backoff_ns == 0xffffffffu) return 0;                    // timing experiment only: no dependency (wrong results)
+#endif
     uint32_t mine = 0;                                          // per-lane partial sum, reduced once at the end
     int look = tile - 1;
     for (;;) {

@@ -34,8 +34,8 @@ template <int TILE> struct F4 {
     static constexpr int OFF_POS = OFF_BC + 2 * NW * 8;         // u16[2][PCAP]
     static constexpr int OFF_MISC = OFF_POS + 2 * PCAP * 2;
     static constexpr int SMEM = OFF_MISC + 256;
-    static constexpr int MINB = TILE >= 16384 ? 4 : 7;   // CTAs per SM the register budget is cut for
-    // misc (u32 index): [0..11] warp counts; per stage st = 0/1 at 16 + 8 st: {tile, stream, tile in stream, total,
+    static constexpr int MINB = TILE >= 32768 ? 2 : (TILE >= 16384 ? 4 : 7);   // CTAs per SM the register budget is cut for
+    // misc (u32 index): [0..23] warp counts; per stage st = 0/1 at 24 + 8 st: {tile, stream, tile in stream, total,
     // halo total, k0}; bytes 192..: mbarriers full[2], go[2], done[2]
 };
 
@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(F4<TILE>::NT, F4<TILE>::MINB) k_frame4(const _
     BatchState *S = b.state;
 
     auto issue = [&](uint32_t t, uint32_t stg) {         // thread 0: geometry of ticket t, TMA copy of its window
-        uint32_t *m = s_misc + 16 + 8 * stg;
+        uint32_t *m = s_misc + 24 + 8 * stg;
         m[0] = t;
         if (t >= total_tiles) return;
         int s;
@@ -104,13 +104,13 @@ __global__ void __launch_bounds__(F4<TILE>::NT, F4<TILE>::MINB) k_frame4(const _
         for (uint32_t j = 0;; ++j) {
             const uint32_t stg = j & 1u, par = (j >> 1) & 1u;
             mbar_wait(bar_go + 8u * stg, par);
-            const uint32_t *m = s_misc + 16 + 8 * stg;
+            const uint32_t *m = s_misc + 24 + 8 * stg;
             const uint32_t lt = m[2], total = m[3];
             if (lt == F4_EXIT) return;
             const int s = (int)m[1];
             const uint32_t base = lookback_wide(b.st[s].status_frame, (int)lt, total, lane, backoff_ns);
             if (lane == 0) {
-                s_misc[16 + 8 * stg + 5] = base;
+                s_misc[24 + 8 * stg + 5] = base;
                 if ((u64)lt * TILE + TILE > (u64)b.st[s].n) S->n_lines[s] = base + total;   // the tile holding position n
                 mbar_arrive(bar_done + 8u * stg);
             }
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(F4<TILE>::NT, F4<TILE>::MINB) k_frame4(const _
 
     // ---------------- worker warps ----------------
     auto make_tile = [&](uint32_t stg) {
-        const uint32_t *m = s_misc + 16 + 8 * stg;
+        const uint32_t *m = s_misc + 24 + 8 * stg;
         const int s = (int)m[1];
         F2Tile T;
         T.data = b.st[s].data;
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(F4<TILE>::NT, F4<TILE>::MINB) k_frame4(const _
     // records of the tile in stage stg (scanned in the previous iteration), outputs at the RAW record index
     auto parse = [&](uint32_t stg, uint32_t par) {
         mbar_wait(bar_done + 8u * stg, par);                    // k0 from the look-back warp
-        const uint32_t *m = s_misc + 16 + 8 * stg;
+        const uint32_t *m = s_misc + 24 + 8 * stg;
         const int s = (int)m[1];
         const uint32_t lt = m[2], total = m[3], k0 = m[5];
         const StreamDev &st = b.st[s];
@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(F4<TILE>::NT, F4<TILE>::MINB) k_frame4(const _
 #pragma unroll 1
     for (;; ++j) {
         const uint32_t stg = j & 1u;
-        uint32_t *m = s_misc + 16 + 8 * stg;
+        uint32_t *m = s_misc + 24 + 8 * stg;
         if (m[0] >= total_tiles) break;
         const int s = (int)m[1];
         const uint32_t lt = m[2];
@@ -298,7 +298,7 @@ __global__ void __launch_bounds__(F4<TILE>::NT, F4<TILE>::MINB) k_frame4(const _
         for (int i = 0; i < 8; ++i) atomicAdd(&g_f3_prof[(tid >> 5) * 8 + i], (unsigned long long)prof[i]);
 #endif
     if (tid == 0) {                                             // release the look-back warp
-        s_misc[16 + 8 * (j & 1u) + 2] = F4_EXIT;
+        s_misc[24 + 8 * (j & 1u) + 2] = F4_EXIT;
         mbar_arrive(bar_go + 8u * (j & 1u));
     }
 }

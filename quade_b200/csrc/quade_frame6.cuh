@@ -1,0 +1,382 @@
+// quade_frame6.cuh -- K1 k_frame6: dependency-free framing (included by quade_kernels.cu after quade_frame2/3.cuh)
+//
+// What every single-pass variant before it (k_frame2 .. k_frame5) was bound by, measured with clock64 probes
+// (tools/probe_f3prof.py): the decoupled look-back for a tile's global line index k0 takes ~5 us per tile -- not
+// the L2 round trips but the wait for the slowest of the several hundred predecessor tiles in flight to publish
+// its line count (a running maximum over a jittery ticket -> copy -> scan latency).  Scan warps sat idle 79 % of
+// the time.  k0 is needed for two things only:
+//   (a) k0 mod 4: which line ends close a record.  GUESSED from the text -- the first line end i in 0..3 whose
+//       next line starts with '@' and whose third next line starts with '+' (exact for well-formed FASTQ: a
+//       quality line may start with '@', but the line two after it is then a sequence line);
+//   (b) the record index the outputs are stored at.  DEFERRED: a tile reserves room in per-stream scratch arrays
+//       with one atomic and stores its records there in tile order of arrival.
+// So tiles are independent: no look-back, no ordering between CTAs, nothing to wait for.  Afterwards
+//   k_tilescan  one CTA per stream: exclusive scan of the tiles' line counts -> true k0, record base and record
+//               count per tile; a tile whose guess was wrong (or that found no scratch room) goes to a redo list;
+//   k_densify   one warp per tile: scratch -> the dense per-record arrays at the true record index; counts records
+//               with len(seq) != len(qual) and finds the first blank header (FastqReader.py:42,48-50);
+//   k_frame6<true> parses the redo tiles again with the true k0, straight into the dense arrays.
+// The result never depends on the guess; on well-formed input the redo list is empty.
+#pragma once
+
+namespace quade {
+namespace {
+
+constexpr int F6T = 256;
+constexpr uint32_t F6_BLANK = 1u << 25;        // scratch digest: the header had no name token
+
+template <bool REDO>
+__global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ BatchDev b, uint32_t total_tiles)
+{
+    extern __shared__ __align__(128) uint8_t f6_smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t sm0 = smem_u32(f6_smem);
+    const u64 *s_bm = reinterpret_cast<const u64 *>(f6_smem + F3_OFF_BM);
+    const u64 *s_bc = reinterpret_cast<const u64 *>(f6_smem + F3_OFF_BC);
+    uint16_t *s_pos = reinterpret_cast<uint16_t *>(f6_smem + F3_OFF_POS);
+    uint32_t *s_misc = reinterpret_cast<uint32_t *>(f6_smem + F3_OFF_MISC);
+    const uint32_t s_bar = sm0 + F3_OFF_MISC + 64, a_pos = sm0 + F3_OFF_POS;
+    BatchState *S = b.state;
+    const uint32_t n_todo = REDO ? min(S->n_redo, b.redo_cap) : total_tiles;
+
+    auto take = [&]() {                                  // thread 0: next ticket, geometry, TMA copy of the window
+        const uint32_t t = atomicAdd(REDO ? &S->ticket_redo : &S->ticket_frame, 1u);
+        s_misc[10] = t;
+        if (t >= n_todo) return;
+        int s = 0;
+        uint32_t lt;
+        if (REDO) {
+            const uint32_t packed = b.redo_list[t];
+            s = (int)(packed >> 28);
+            lt = packed & 0x0fffffffu;
+        } else {
+#pragma unroll
+            for (int i = 1; i < kMaxStreams; ++i) s += (i < b.n_streams && t >= b.frame_tile_start[i]) ? 1 : 0;
+            lt = t - b.frame_tile_start[s];
+        }
+        s_misc[11] = (uint32_t)s;
+        s_misc[12] = lt;
+        const uint32_t tbase = lt * (uint32_t)F2_TILE, n16 = (b.st[s].n + 15u) & ~15u;
+        const uint32_t bytes = n16 > tbase ? min((uint32_t)F2_WIN, n16 - tbase) : 0u;
+        if (bytes) {
+            fence_proxy_async();
+            mbar_expect_tx(s_bar, bytes);
+            bulk_g2s(sm0, b.st[s].data + tbase, bytes, s_bar);
+        }
+    };
+    if (tid == 0) {
+        mbar_init(s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        take();
+    }
+    __syncthreads();
+    uint32_t phase = 0;
+
+    for (;;) {
+        const uint32_t tile = s_misc[10];
+        if (tile >= n_todo) break;
+        const int s = (int)s_misc[11];
+        const uint32_t lt = s_misc[12];
+        const StreamDev &st = b.st[s];
+        F2Tile T;
+        T.data = st.data;
+        T.sdata = sm0;
+        T.bm = s_bm;
+        T.bc = s_bc;
+        T.tbase = lt * (uint32_t)F2_TILE;
+        T.cap = (uint32_t)F2_WIN;
+        T.n = st.n;
+        T.win = T.n > T.tbase ? min((uint32_t)F2_WIN, T.n - T.tbase) : 0u;
+        T.last = ((b.last >> s) & 1) != 0;
+        if (((T.n + 15u) & ~15u) > T.tbase) {                   // a copy was issued for this tile
+            while (!mbar_try_wait(s_bar, phase)) {}
+            phase ^= 1u;
+        }
+
+        // 1. newline / candidate masks: thread t takes the 16-byte chunks t, t+256, ... (conflict-free 128-bit
+        //    loads); the 16-bit masks stored per chunk ARE the 64-bit bitmap words
+        {
+            const bool edge = T.win < (uint32_t)F2_WIN;         // the window reaches the end of the buffer
+            uint32_t vbit = F2_NONE;                            // window offset of a virtual last line end
+            if (edge && T.last && T.n > 0u && T.n - T.tbase < (uint32_t)F2_WIN) vbit = T.n - T.tbase;
+#pragma unroll
+            for (uint32_t i = 0; i < 5; ++i) {
+                const uint32_t c = (uint32_t)tid + (uint32_t)F6T * i, off = 16u * c;
+                if (i == 4 && tid >= F2_HALO / 16) break;       // halo: 128 chunks, warps 0-3
+                const uint4 q = lds128(sm0 + off);
+                uint32_t m = f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w));
+                uint32_t cd = f2_gather16(f2_c_flags(q.x), f2_c_flags(q.y), f2_c_flags(q.z), f2_c_flags(q.w));
+                if (edge) {
+                    const uint32_t keep = off >= T.win ? 0u : (T.win - off >= 16u ? 0xffffu : (1u << (T.win - off)) - 1u);
+                    m &= keep;
+                    cd &= keep;
+                    if ((vbit >> 4) == c && f2_byte(T, T.n - 1u) != '\n') m |= 1u << (vbit & 15u);   // no final '\n'
+                }
+                sts16(sm0 + F3_OFF_BM + 2u * c, m);
+                sts16(sm0 + F3_OFF_BC + 2u * c, cd);
+            }
+        }
+        __syncthreads();                                        // B1: bitmaps complete
+
+        // 2. line ends per thread (64 bytes = bitmap word tid), warp scans; the halo's 32 words by warp 1
+        const u64 mine = s_bm[tid];
+        const uint32_t cnt = (uint32_t)__popcll(mine);
+        uint32_t inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += x;
+        }
+        if (lane == 31) s_misc[warp] = inc;
+        u64 hm = 0;
+        uint32_t hinc = 0, hcnt = 0;
+        if (warp == 1) {
+            hm = s_bm[F6T + lane];
+            hcnt = (uint32_t)__popcll(hm);
+            hinc = hcnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t x = __shfl_up_sync(0xffffffffu, hinc, o);
+                if (lane >= o) hinc += x;
+            }
+            if (lane == 31) s_misc[8] = hinc;
+        }
+        __syncthreads();                                        // B2: warp counts
+        const uint4 wa = *reinterpret_cast<const uint4 *>(s_misc), wb = *reinterpret_cast<const uint4 *>(s_misc + 4);
+        const uint32_t c1 = wa.x, c2 = c1 + wa.y, c3 = c2 + wa.z, c4 = c3 + wa.w, c5 = c4 + wb.x, c6 = c5 + wb.y,
+                       c7 = c6 + wb.z, total = c7 + wb.w;
+        uint32_t before = 0u;
+        before = warp == 1 ? c1 : before;
+        before = warp == 2 ? c2 : before;
+        before = warp == 3 ? c3 : before;
+        before = warp == 4 ? c4 : before;
+        before = warp == 5 ? c5 : before;
+        before = warp == 6 ? c6 : before;
+        before = warp == 7 ? c7 : before;
+        const uint32_t npos = min(total + s_misc[8], (uint32_t)F3_PCAP);
+
+        // 3. dense list of the window's line ends (tile, then halo: list order = byte order)
+        {
+            uint32_t i = before + inc - cnt;
+            uint32_t lo = (uint32_t)mine, hi = (uint32_t)(mine >> 32);
+            const uint32_t o0 = (uint32_t)tid * 64u;
+            while (lo) {
+                const uint32_t bit = (uint32_t)__ffs((int)lo) - 1u;
+                lo &= lo - 1u;
+                if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(o0 + bit);
+                ++i;
+            }
+            while (hi) {
+                const uint32_t bit = (uint32_t)__ffs((int)hi) - 1u;
+                hi &= hi - 1u;
+                if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(o0 + 32u + bit);
+                ++i;
+            }
+            if (warp == 1) {
+                i = total + hinc - hcnt;
+                const uint32_t h0 = (uint32_t)(F6T + lane) * 64u;
+                while (hm) {
+                    const uint32_t bit = (uint32_t)__ffsll((long long)hm) - 1u;
+                    hm &= hm - 1ull;
+                    if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(h0 + bit);
+                    ++i;
+                }
+            }
+        }
+        __syncthreads();                                        // B3: list complete
+
+        // 4. which list entries close a record: the true k0 (redo) or the guess from the text
+        const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
+        uint32_t t0 = 3u, k0 = 0u;                              // list index of the first record-closing line
+        if (REDO) {
+            k0 = st.tile_tab[lt].x;
+            t0 = (3u - k0) & 3u;
+        } else if (lt != 0u) {
+            bool ok = false;
+            if (lane < 4 && (uint32_t)lane + 2u < npos)
+                ok = lds8(sm0 + lds16(a_pos + 2u * lane) + 1u) == '@' && lds8(sm0 + lds16(a_pos + 2u * (lane + 2)) + 1u) == '+';
+            const unsigned g = __ballot_sync(0xffffffffu, ok);
+            t0 = g ? (uint32_t)__ffs((int)g) - 1u : 0u;
+        }
+        const uint32_t nslot = first + (total > t0 ? (total - t0 + 3u) >> 2 : 0u);
+        const uint32_t rbase = lt == 0u ? 0u : (k0 >> 2) + 1u;  // REDO: record index of slot 0
+        if (!REDO && tid == 0) {                                // room in the scratch arrays, in tile order of arrival
+            uint32_t sb = nslot ? atomicAdd(&S->scratch_cursor[s], nslot) : 0u;
+            if ((u64)sb + nslot > (u64)st.cap_rec || total + s_misc[8] > (uint32_t)F3_PCAP) sb = F2_NONE;   // -> redo
+            s_misc[9] = sb;
+            st.tile_tab[lt] = make_uint4(total, t0, nslot, sb);
+        }
+
+        // record of slot i (FastqReader.py:37-44); false: only the redo pass can find it (line-end list overflow)
+        auto parse_slot = [&](uint32_t slot, F2Rec &R) -> bool {
+            if (first && slot == 0u) { R = f2_parse(T, 0u, s_pos, 0u, npos); return true; }
+            const uint32_t ti = t0 + 4u * (slot - first);
+            if (ti < npos) { R = f2_parse(T, T.tbase + s_pos[ti] + 1u, s_pos, ti + 1u, npos); return true; }
+            R.complete = R.valid = false;
+            R.name_off = R.nlen = R.seq_off = R.qual_off = R.seq_len = R.end = 0u;
+            if (!REDO) return false;
+            const uint32_t want = (rbase + slot) * 4u - 1u;     // more than F3_PCAP lines in 18 KiB: bitmap search
+            uint32_t k = k0, ppos = T.tbase, e = F2_NONE;
+            while (k <= want) {
+                e = f2_next_nl(T, ppos);
+                if (e == F2_NONE) break;
+                ppos = e + 1u;
+                ++k;
+            }
+            if (e != F2_NONE) R = f2_parse(T, e + 1u, s_pos, 0u, 0u);
+            return true;
+        };
+        // redo pass: outputs at the raw record index, as k_frame2.  First pass: the same fields at scratch position
+        // v; an index read with a blank header carries F6_BLANK in its digest (insert reads: name length 0).
+        auto store = [&](uint32_t v, const F2Rec &R) {
+            if (!R.complete) return;
+            const uint32_t inv = R.valid ? 0u : 0x80000000u;
+            if (REDO) {
+                if (v >= st.cap_rec) { S->err_capacity = 1u; return; }
+                if (R.nlen == 0u) atomicMax(&S->first_blank[s], ~v);           // keeps the LOWEST blank record index
+                if (inv) atomicAdd(&S->n_invalid[s], 1u);
+                st.vend[v] = R.end;
+                if (s < 2) {
+                    st.rec[v] = make_uint4(R.name_off, R.seq_off, R.qual_off, R.seq_len | inv);
+                    st.vnlen[v] = R.nlen;
+                } else if (inv) {
+                    st.dig[v] = make_uint4(0u, 0u, 0u, inv);
+                } else {
+                    f2_digest(b, st, s, T, R, v);
+                }
+            } else {
+                st.vend_t[v] = R.end;
+                if (s < 2) {
+                    st.rec_t[v] = make_uint4(R.name_off, R.seq_off, R.qual_off, R.seq_len | inv);
+                    st.vnlen_t[v] = R.nlen;
+                } else if (inv) {
+                    st.dig_t[v] = make_uint4(0u, 0u, 0u, inv | (R.nlen == 0u ? F6_BLANK : 0u));
+                } else {
+                    StreamDev stt = st;
+                    stt.dig = st.dig_t;
+                    stt.sfx = st.sfx_t;
+                    f2_digest(b, stt, s, T, R, v);
+                    if (R.nlen == 0u) st.dig_t[v].w |= F6_BLANK;
+                }
+            }
+        };
+
+        // 5. one thread per record; the first one is parsed while the scratch reservation is in flight
+        F2Rec R;
+        bool have = false;
+        if ((uint32_t)tid < nslot) have = parse_slot((uint32_t)tid, R);
+        __syncthreads();                                        // B4: scratch base known
+        const uint32_t base = REDO ? rbase : s_misc[9];
+        if (base != F2_NONE) {
+            if (have) store(base + (uint32_t)tid, R);
+            for (uint32_t slot = (uint32_t)tid + F6T; slot < nslot; slot += F6T)
+                if (parse_slot(slot, R)) store(base + slot, R);
+        }
+        __syncthreads();                                        // B5: window, bitmaps and list are free
+        if (tid == 0) take();
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// k_tilescan: one CTA per stream.  tile_tab[t] = {line ends, guessed t0, records, scratch base} becomes
+// {k0, ok, records, scratch base}; n_lines; tiles to parse again are appended to the redo list.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) k_tilescan(const __grid_constant__ BatchDev b)
+{
+    __shared__ uint32_t s_warp[33];
+    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const StreamDev &st = b.st[s];
+    BatchState *S = b.state;
+    const uint32_t n_t = st.n ? st.n / (uint32_t)F2_TILE + 1u : 0u;
+    const uint32_t run = (n_t + 1023u) / 1024u;
+    const uint32_t t_lo = min(n_t, (uint32_t)tid * run), t_hi = min(n_t, t_lo + run);
+    uint32_t sum = 0;
+    for (uint32_t t = t_lo; t < t_hi; ++t) sum += st.tile_tab[t].x;
+    uint32_t inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += x;
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        const uint32_t w = s_warp[lane];
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t x = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += x;
+        }
+        s_warp[lane] = wi - w;
+        if (lane == 31) s_warp[32] = wi;
+    }
+    __syncthreads();
+    uint32_t k0 = s_warp[warp] + inc - sum;
+    if (tid == 0) S->n_lines[s] = s_warp[32];
+    for (uint32_t t = t_lo; t < t_hi; ++t) {
+        const uint4 e = st.tile_tab[t];
+        const uint32_t total = e.x, first = t == 0u ? 1u : 0u;
+        const uint32_t nslot = ((k0 + total) >> 2) - (k0 >> 2) + first;
+        const bool ok = nslot == 0u || (e.y == ((3u - k0) & 3u) && e.w != F2_NONE);
+        st.tile_tab[t] = make_uint4(k0, ok ? 1u : 0u, nslot, e.w);
+        if (!ok) {
+            const uint32_t idx = atomicAdd(&S->n_redo, 1u);
+            if (idx < b.redo_cap) b.redo_list[idx] = (uint32_t)s << 28 | t;
+        }
+        k0 += total;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// k_densify: one warp per tile, scratch -> dense per-record arrays at the true record index (the pairing ordinal
+// of a file without invalid records).  Counts the records with len(seq) != len(qual), finds the first blank header.
+// ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_densify(const __grid_constant__ BatchDev b, uint32_t total_tiles)
+{
+    const int lane = threadIdx.x & 31;
+    BatchState *S = b.state;
+    const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
+    for (uint32_t tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < total_tiles; tile += nwarps) {
+        int s = 0;
+#pragma unroll
+        for (int i = 1; i < kMaxStreams; ++i) s += (i < b.n_streams && tile >= b.frame_tile_start[i]) ? 1 : 0;
+        const uint32_t lt = tile - b.frame_tile_start[s];
+        const StreamDev &st = b.st[s];
+        const uint4 e = st.tile_tab[lt];
+        if (!(e.y & 1u) || e.z == 0u) continue;
+        const uint32_t rbase = lt == 0u ? 0u : (e.x >> 2) + 1u, n_rec = S->n_lines[s] >> 2, sv = st.sfx_slot >> 4;
+        for (uint32_t i = lane; i < e.z; i += 32) {
+            const uint32_t j = rbase + i, v = e.w + i;
+            if (j >= n_rec) continue;                           // trailing partial record (FastqReader.py:57-58)
+            if (j >= st.cap_rec) { S->err_capacity = 1u; continue; }
+            st.vend[j] = st.vend_t[v];
+            bool blank, inv;
+            if (s < 2) {
+                const uint4 r = st.rec_t[v];
+                const uint32_t nl = st.vnlen_t[v];
+                st.rec[j] = r;
+                st.vnlen[j] = nl;
+                blank = nl == 0u;
+                inv = (r.w >> 31) != 0u;
+            } else {
+                uint4 d = st.dig_t[v];
+                blank = (d.w & F6_BLANK) != 0u;
+                inv = (d.w >> 31) != 0u;
+                d.w &= ~F6_BLANK;
+                st.dig[j] = d;
+                if (!inv) {
+                    const uint4 *src = reinterpret_cast<const uint4 *>(st.sfx_t + (size_t)v * st.sfx_slot);
+                    uint4 *dst = reinterpret_cast<uint4 *>(st.sfx + (size_t)j * st.sfx_slot);
+                    for (uint32_t q = 0; q < sv; ++q) dst[q] = src[q];
+                }
+            }
+            if (blank) atomicMax(&S->first_blank[s], ~j);       // keeps the LOWEST blank record index
+            if (inv) atomicAdd(&S->n_invalid[s], 1u);
+        }
+    }
+}
+
+} // namespace
+} // namespace quade

@@ -315,6 +315,8 @@ __global__ void __launch_bounds__(FT) k_frame(const __grid_constant__ BatchDev b
 #include "quade_frame2.cuh"
 #include "quade_frame3.cuh"
 #include "quade_frame4.cuh"
+#include "quade_frame5.cuh"
+#include "quade_frame6.cuh"
 #include "quade_kernels3.cuh"
 #include "quade_compact.cuh"
 #include "quade_compact3.cuh"

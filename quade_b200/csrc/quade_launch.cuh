@@ -10,6 +10,7 @@ void set_compact_variant(int v) { g_compact_variant = v; }
 static int g_frame_variant = 2, g_occ_frame2 = 0, g_occ_frame3 = 0;   // 3 = k_frame3 (opt-in for now)
 void set_frame_variant(int v) { g_frame_variant = v; }
 int frame_variant() { return g_frame_variant; }
+int frame_launches() { return g_frame_variant == 10 ? 4 : 1; }
 
 static void init_launch_config()
 {
@@ -68,6 +69,65 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
         if (g4 > tiles) g4 = tiles;
         if (g_frame_variant == 4) k_frame4<16384><<<g4, F4<16384>::NT, F4<16384>::SMEM, s>>>(b, tiles, (uint32_t)backoff);
         else k_frame4<8192><<<g4, F4<8192>::NT, F4<8192>::SMEM, s>>>(b, tiles, (uint32_t)backoff);
+        return;
+    }
+    if (g_frame_variant == 10) {                               // k_frame6: independent tiles, scan + densify after
+        static int occ6 = 0;
+        if (!occ6) {
+            cudaFuncSetAttribute(k_frame6<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
+            cudaFuncSetAttribute(k_frame6<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ6, k_frame6<false>, F6T, F3_SMEM);
+            if (occ6 < 1) occ6 = 1;
+        }
+        uint32_t g6 = (uint32_t)(g_sms * occ6);
+        if (g6 > total) g6 = total;
+        k_frame6<false><<<g6, F6T, F3_SMEM, s>>>(b, total);
+        k_tilescan<<<b.n_streams, 1024, 0, s>>>(b);
+        k_densify<<<(uint32_t)g_sms * 4u, 256, 0, s>>>(b, total);
+        k_frame6<true><<<(uint32_t)g_sms, F6T, F3_SMEM, s>>>(b, total);
+        return;
+    }
+    if (g_frame_variant >= 7 && g_frame_variant <= 9) {        // k_frame5: scan / look-back / parse warps
+        static int backoff = -1, occ[3] = {0, 0, 0};
+        auto k7 = k_frame5<16384, 2, 4>;
+        auto k8 = k_frame5<16384, 3, 3>;
+        auto k9 = k_frame5<16384, 4, 3>;
+        using G7 = F5<16384, 2>;
+        using G8 = F5<16384, 3>;
+        using G9 = F5<16384, 4>;
+        if (backoff < 0) {
+            const char *v = getenv("QUADE_F3_BACKOFF");
+            backoff = v ? atoi(v) : 256;
+            cudaFuncSetAttribute(k7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G7::SMEM);
+            cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G8::SMEM);
+            cudaFuncSetAttribute(k9, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G9::SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[0], k7, G7::NT, G7::SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[1], k8, G8::NT, G8::SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ[2], k9, G9::NT, G9::SMEM);
+        }
+        uint32_t tiles = 0;
+        for (int i = 0; i < b.n_streams; ++i) tiles += b.st[i].n ? b.st[i].n / 16384u + 1u : 0u;
+        const int v = g_frame_variant - 7;
+        uint32_t g5 = (uint32_t)(g_sms * max(1, occ[v]));
+        if (g5 > tiles) g5 = tiles;
+        if (v == 0) k7<<<g5, G7::NT, G7::SMEM, s>>>(b, tiles, (uint32_t)backoff);
+        else if (v == 1) k8<<<g5, G8::NT, G8::SMEM, s>>>(b, tiles, (uint32_t)backoff);
+        else k9<<<g5, G9::NT, G9::SMEM, s>>>(b, tiles, (uint32_t)backoff);
+        return;
+    }
+    if (g_frame_variant == 6) {                                // 32 KiB tiles
+        static int backoff = -1, occ32 = 0;
+        if (backoff < 0) {
+            const char *v = getenv("QUADE_F3_BACKOFF");
+            backoff = v ? atoi(v) : 256;
+            cudaFuncSetAttribute(k_frame4<32768>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F4<32768>::SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ32, k_frame4<32768>, F4<32768>::NT, F4<32768>::SMEM);
+        }
+        uint32_t tiles = 0;
+        for (int i = 0; i < b.n_streams; ++i) tiles += b.st[i].n ? b.st[i].n / 32768u + 1u : 0u;
+        uint32_t g4 = (uint32_t)(g_sms * max(1, occ32));
+        if (g4 > tiles) g4 = tiles;
+        k_frame4<32768><<<g4, F4<32768>::NT, F4<32768>::SMEM, s>>>(b, tiles, (uint32_t)backoff);
         return;
     }
     if (g_frame_variant == 3) {

@@ -22,6 +22,11 @@ for rep in range(3):
     names = (["tma wait", "masks+B1", "scan+B2", "list+B3", "lookback|parse", "B4 wait", "store+B5", "take+B6"] if os.environ["QUADE_FRAME"] == "3"
              else ["tma wait", "masks+bar", "scan+bar", "publish+list", "k0 wait", "parse+store", "bar", "issue+bar"])
     tile_bytes = 8192 if os.environ["QUADE_FRAME"] == "5" else 16384
+    if int(os.environ["QUADE_FRAME"]) >= 7:
+        tiles = sum(sizes) / 16384
+        nm = ["scan:full wait", "scan:work", "lb:go wait", "lb:lookback", "parse:listed wait", "parse:k0 wait", "parse:work", "parse:take"]
+        print("rep", rep, "frame ms %.3f" % r.ms_kernel["frame"], " | ".join("%s %.0f" % (n, x / tiles) for n, x in zip(nm, v[:8])), "(cycles per tile)")
+        continue
     for w in range(2):
         tot = sum(v[w * 8:w * 8 + 8])
         print("rep", rep, "warp", w, "frame ms %.3f" % r.ms_kernel["frame"], " ".join("%s %.1f%%" % (n, 100.0 * x / tot) for n, x in zip(names, v[w * 8:w * 8 + 8])), "cycles/tile %.0f" % (tot / (sum(sizes) / tile_bytes)))
