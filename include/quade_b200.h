@@ -99,6 +99,7 @@ typedef struct {
     uint64_t in_bytes;         /* sum of consumed[] */
     uint64_t out_bytes;        /* bin_off[0][nbins] + bin_off[1][nbins] */
     uint64_t gpu_launches;     /* kernels launched for this batch */
+    uint64_t reframed_tiles;   /* 16 KiB tiles framed a second time: their text defeated the record-start guess */
 } quade_result;
 
 int quade_version(void);

@@ -34,7 +34,7 @@ class Result(C.Structure):
                 ("counters", C.c_void_p), ("nbins", C.c_int32), ("err", C.c_int32),
                 ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
                 ("ms_kernel", C.c_float * K_COUNT), ("in_bytes", C.c_uint64), ("out_bytes", C.c_uint64),
-                ("gpu_launches", C.c_uint64)]
+                ("gpu_launches", C.c_uint64), ("reframed_tiles", C.c_uint64)]
 
 
 class SynthParams(C.Structure):

@@ -126,7 +126,7 @@ void launch_fix(const BatchDev &b, cudaStream_t s);
 void launch_pairing2(const BatchDev &b, cudaStream_t s);
 void launch_classify2(const BatchDev &b, cudaStream_t s);
 void set_frame_variant(int v);
-int frame_variant();     // 2 = fused TMA-staged k_frame2 + digest classify (default), 1 = k_frame/k_validate/k_classify
+int frame_variant();     // 10 = k_frame6 + k_tilescan + k_densify (default), 2..9 = look-back variants, 1 = k_frame/k_validate/k_classify
 void launch_validate(const BatchDev &b, cudaStream_t s);
 void launch_pairing(const BatchDev &b, cudaStream_t s);
 void launch_classify(const BatchDev &b, cudaStream_t s);

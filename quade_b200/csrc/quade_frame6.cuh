@@ -292,7 +292,8 @@ __global__ void __launch_bounds__(1024) k_tilescan(const __grid_constant__ Batch
     const uint32_t run = (n_t + 1023u) / 1024u;
     const uint32_t t_lo = min(n_t, (uint32_t)tid * run), t_hi = min(n_t, t_lo + run);
     uint32_t sum = 0;
-    for (uint32_t t = t_lo; t < t_hi; ++t) sum += st.tile_tab[t].x;
+#pragma unroll 8
+    for (uint32_t t = t_lo; t < t_hi; ++t) sum += st.tile_tab[t].x;             // independent loads: 8 in flight
     uint32_t inc = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -315,17 +316,25 @@ __global__ void __launch_bounds__(1024) k_tilescan(const __grid_constant__ Batch
     __syncthreads();
     uint32_t k0 = s_warp[warp] + inc - sum;
     if (tid == 0) S->n_lines[s] = s_warp[32];
-    for (uint32_t t = t_lo; t < t_hi; ++t) {
-        const uint4 e = st.tile_tab[t];
-        const uint32_t total = e.x, first = t == 0u ? 1u : 0u;
-        const uint32_t nslot = ((k0 + total) >> 2) - (k0 >> 2) + first;
-        const bool ok = nslot == 0u || (e.y == ((3u - k0) & 3u) && e.w != F2_NONE);
-        st.tile_tab[t] = make_uint4(k0, ok ? 1u : 0u, nslot, e.w);
-        if (!ok) {
-            const uint32_t idx = atomicAdd(&S->n_redo, 1u);
-            if (idx < b.redo_cap) b.redo_list[idx] = (uint32_t)s << 28 | t;
+    for (uint32_t tb = t_lo; tb < t_hi; tb += 8u) {            // 8 entries loaded at once, then stored
+        uint4 ev[8];
+#pragma unroll
+        for (uint32_t q = 0; q < 8; ++q) ev[q] = tb + q < t_hi ? st.tile_tab[tb + q] : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (uint32_t q = 0; q < 8; ++q) {
+            const uint32_t t = tb + q;
+            if (t >= t_hi) break;
+            const uint4 e = ev[q];
+            const uint32_t total = e.x, first = t == 0u ? 1u : 0u;
+            const uint32_t nslot = ((k0 + total) >> 2) - (k0 >> 2) + first;
+            const bool ok = nslot == 0u || (e.y == ((3u - k0) & 3u) && e.w != F2_NONE);
+            st.tile_tab[t] = make_uint4(k0, ok ? 1u : 0u, nslot, e.w);
+            if (!ok) {
+                const uint32_t idx = atomicAdd(&S->n_redo, 1u);
+                if (idx < b.redo_cap) b.redo_list[idx] = (uint32_t)s << 28 | t;
+            }
+            k0 += total;
         }
-        k0 += total;
     }
 }
 

@@ -7,7 +7,7 @@ namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 static int g_sms = 0, g_occ_frame = 0, g_occ_validate = 0, g_occ_compact = 0, g_occ_compact3 = 0, g_compact_variant = 3;
 void set_compact_variant(int v) { g_compact_variant = v; }
-static int g_frame_variant = 2, g_occ_frame2 = 0, g_occ_frame3 = 0;   // 3 = k_frame3 (opt-in for now)
+static int g_frame_variant = 10, g_occ_frame2 = 0, g_occ_frame3 = 0;  // 10 = k_frame6 (default); 2..9: earlier single-pass variants
 void set_frame_variant(int v) { g_frame_variant = v; }
 int frame_variant() { return g_frame_variant; }
 int frame_launches() { return g_frame_variant == 10 ? 4 : 1; }

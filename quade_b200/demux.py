@@ -26,6 +26,7 @@ class DemuxResult:
         self.ms_kernel = {n: float(raw.ms_kernel[i]) for i, n in enumerate(_lib.K_NAMES)}
         self.in_bytes, self.out_bytes = int(raw.in_bytes), int(raw.out_bytes)
         self.gpu_launches = int(raw.gpu_launches)
+        self.reframed_tiles = int(raw.reframed_tiles)
 
     def arena(self, read):
         """Host view (no copy) of one output arena; valid until the slot is reused."""

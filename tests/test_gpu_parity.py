@@ -166,3 +166,67 @@ def test_per_stream_eof_flags_match_oracle_batch_by_batch():
             break
     assert total == n
     ctx.close()
+
+
+def _mutate_records(stream, rng, frac, fn):
+    """Apply fn(lines[4]) -> lines[4] to a random fraction of the 4-line records of one FASTQ byte stream."""
+    lines = stream.split(b"\n")
+    tail = lines[-1]
+    lines = lines[:-1]
+    for j in range(0, len(lines) - 3, 4):
+        if rng.random() < frac:
+            lines[j:j + 4] = fn(lines[j:j + 4])
+    return b"\n".join(lines) + b"\n" + tail
+
+
+@pytest.mark.parametrize("variant", ["headers_without_at", "plus_line_text", "qual_starts_at", "invalid_and_crlf", "tiny_lines"])
+def test_multi_tile_malformed_text_matches_oracle(variant):
+    """Many 16 KiB tiles per file whose text defeats any guess about where a record starts: headers that do not
+    start with '@' (the reference drops the first byte whatever it is, FastqReader.py:42), third lines that are
+    not '+' (ignored by the reference, :43), quality strings starting with '@' or '+', records skipped for
+    len(seq) != len(qual) in one file only (:48-50), CRLF, and a stretch of very short lines (line-end list
+    overflow).  The GPU framing must not depend on what the text looks like."""
+    from quade_b200.synth import Synth
+    s = Synth.from_config("cfg3")
+    n = 12000
+    streams = [bytes(a) for a in s.generate(3, n)]
+    rng = np.random.default_rng(17)
+
+    def no_at(r):
+        return [b"X" + r[0][1:], r[1], r[2], r[3]]
+
+    def plus_text(r):
+        return [r[0], r[1], b"@" + r[0][1:8], r[3]]             # third line looks like a header
+
+    def qual_at(r):
+        return [r[0], r[1], r[2], (b"@" if rng.random() < 0.5 else b"+") + r[3][1:]]
+
+    def invalid(r):
+        return [r[0], r[1], r[2], r[3][:-1]]                    # len(seq) != len(qual): skipped in this file only
+
+    def crlf(r):
+        return [x + b"\r" for x in r]
+
+    if variant == "headers_without_at":
+        streams = [_mutate_records(x, rng, 0.5, no_at) for x in streams]
+    elif variant == "plus_line_text":
+        streams = [_mutate_records(x, rng, 0.5, plus_text) for x in streams]
+    elif variant == "qual_starts_at":
+        streams = [_mutate_records(x, rng, 0.5, qual_at) for x in streams]
+    elif variant == "invalid_and_crlf":
+        streams = [_mutate_records(x, rng, 0.3, crlf) for x in streams]
+        streams[1] = _mutate_records(streams[1], rng, 0.001, invalid)
+        streams[2] = _mutate_records(streams[2], rng, 0.002, invalid)
+    elif variant == "tiny_lines":
+        tiny = b"".join(b"@t%d\nA\n+\nI\n" % i for i in range(3000))      # ~11 bytes per record, 2 bytes per line
+        streams = [tiny + _mutate_records(x[x.index(b"\n@") + 1:], rng, 0.2, no_at) for x in streams]
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    ref = O.demux_batch(p, streams, last=True)
+    ctx, _ = _ctx_for(p, max_stream_bytes=8 << 20, max_pairs=n + 4096)
+    r = ctx.run(streams, last=True)
+    _assert_same(r, ref, p.nbins, variant)
+    assert ref.n_pairs > 1000
+    import os
+    if os.environ.get("QUADE_FRAME", "10") == "10" and variant in ("headers_without_at", "plus_line_text", "tiny_lines"):
+        assert r.reframed_tiles > 0, "the wrong-guess path was not exercised"
+    ctx.close()

@@ -4,6 +4,6 @@
 pat=$1; tag=$2; shift 2
 mkdir -p gpurun_out
 env "$@" python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_plain.log 2>&1 &&
-env "$@" ncu --set full --clock-control none --import-source on -k regex:"$pat" -s 3 -c 1 \
+env "$@" ncu --set full --clock-control none --import-source on -k regex:"$pat" -s ${NCU_SKIP:-3} -c ${NCU_COUNT:-1} \
     -f -o gpurun_out/${tag} python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_ncu.log 2>&1
 echo "ncu exit $?"; tail -2 gpurun_out/${tag}_ncu.log
