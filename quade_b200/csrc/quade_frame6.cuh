@@ -39,9 +39,11 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
     BatchState *S = b.state;
     const uint32_t n_todo = REDO ? min(S->n_redo, b.redo_cap) : total_tiles;
 
-    auto take = [&]() {                                  // thread 0: next ticket, geometry, TMA copy of the window
+    // thread 0, early in a tile: the NEXT ticket (tiles are independent: nothing orders the tickets), its geometry,
+    // and an L2 prefetch of its window, so that the TMA copy issued once this tile is done hits L2
+    auto ticket_next = [&]() {
         const uint32_t t = atomicAdd(REDO ? &S->ticket_redo : &S->ticket_frame, 1u);
-        s_misc[10] = t;
+        s_misc[13] = t;
         if (t >= n_todo) return;
         int s = 0;
         uint32_t lt;
@@ -54,6 +56,20 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
             for (int i = 1; i < kMaxStreams; ++i) s += (i < b.n_streams && t >= b.frame_tile_start[i]) ? 1 : 0;
             lt = t - b.frame_tile_start[s];
         }
+        s_misc[14] = (uint32_t)s;
+        s_misc[15] = lt;
+        const uint32_t tbase = lt * (uint32_t)F2_TILE, n16 = (b.st[s].n + 15u) & ~15u;
+        const uint32_t bytes = n16 > tbase ? min((uint32_t)F2_WIN, n16 - tbase) : 0u;
+        if (bytes)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b.st[s].data + tbase), "r"(bytes) : "memory");
+    };
+    // thread 0, when the window is free: make the prefetched ticket current and copy its window
+    auto issue_next = [&]() {
+        const uint32_t t = s_misc[13];
+        s_misc[10] = t;
+        if (t >= n_todo) return;
+        const int s = (int)s_misc[14];
+        const uint32_t lt = s_misc[15];
         s_misc[11] = (uint32_t)s;
         s_misc[12] = lt;
         const uint32_t tbase = lt * (uint32_t)F2_TILE, n16 = (b.st[s].n + 15u) & ~15u;
@@ -67,7 +83,8 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
     if (tid == 0) {
         mbar_init(s_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        take();
+        ticket_next();
+        issue_next();
     }
     __syncthreads();
     uint32_t phase = 0;
@@ -154,6 +171,18 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
         before = warp == 6 ? c6 : before;
         before = warp == 7 ? c7 : before;
         const uint32_t npos = min(total + s_misc[8], (uint32_t)F3_PCAP);
+        const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
+        if (tid == 0) {
+            // scratch room for the tile's records, in tile order of arrival: an upper bound over the four possible
+            // record phases (at most one slot too many), so that the atomic flies during the list build and parse
+            if (!REDO) {
+                const uint32_t nres = first + ((total + 3u) >> 2);
+                uint32_t sb = atomicAdd(&S->scratch_cursor[s], nres);
+                if ((u64)sb + nres > (u64)st.cap_rec || total + s_misc[8] > (uint32_t)F3_PCAP) sb = F2_NONE;   // -> redo
+                s_misc[9] = sb;
+            }
+            ticket_next();
+        }
 
         // 3. dense list of the window's line ends (tile, then halo: list order = byte order)
         {
@@ -186,7 +215,6 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
         __syncthreads();                                        // B3: list complete
 
         // 4. which list entries close a record: the true k0 (redo) or the guess from the text
-        const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
         uint32_t t0 = 3u, k0 = 0u;                              // list index of the first record-closing line
         if (REDO) {
             k0 = st.tile_tab[lt].x;
@@ -200,12 +228,7 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
         }
         const uint32_t nslot = first + (total > t0 ? (total - t0 + 3u) >> 2 : 0u);
         const uint32_t rbase = lt == 0u ? 0u : (k0 >> 2) + 1u;  // REDO: record index of slot 0
-        if (!REDO && tid == 0) {                                // room in the scratch arrays, in tile order of arrival
-            uint32_t sb = nslot ? atomicAdd(&S->scratch_cursor[s], nslot) : 0u;
-            if ((u64)sb + nslot > (u64)st.cap_rec || total + s_misc[8] > (uint32_t)F3_PCAP) sb = F2_NONE;   // -> redo
-            s_misc[9] = sb;
-            st.tile_tab[lt] = make_uint4(total, t0, nslot, sb);
-        }
+        if (!REDO && tid == 0) st.tile_tab[lt] = make_uint4(total, t0, nslot, s_misc[9]);
 
         // record of slot i (FastqReader.py:37-44); false: only the redo pass can find it (line-end list overflow)
         auto parse_slot = [&](uint32_t slot, F2Rec &R) -> bool {
@@ -273,7 +296,7 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
                 if (parse_slot(slot, R)) store(base + slot, R);
         }
         __syncthreads();                                        // B5: window, bitmaps and list are free
-        if (tid == 0) take();
+        if (tid == 0) issue_next();
         __syncthreads();
     }
 }

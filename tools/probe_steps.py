@@ -22,3 +22,4 @@ for rep in range(3):
         a = time.perf_counter(); r = ctx.collect(); tc.append(time.perf_counter() - a)
     torch.cuda.synchronize(); dt = time.perf_counter() - t0
     print("rep", rep, "total ms/step %.3f" % (dt / 8 * 1e3), "submit ms", [round(x * 1e3, 2) for x in ts], "collect ms", [round(x * 1e3, 2) for x in tc], "kernels", round(r.ms_kernels, 3), {k: round(v, 3) for k, v in r.ms_kernel.items()})
+print("reframed_tiles", r.reframed_tiles)
