@@ -25,6 +25,75 @@ namespace {
 constexpr int F6T = 256;
 constexpr uint32_t F6_BLANK = 1u << 25;        // scratch digest: the header had no name token
 
+// ---- record parser without the candidate bitmap ------------------------------------------------------------
+// k_frame2..5 keep a second bitmap (bytes <= 0x20) for every input byte so that the record threads can hop over
+// name tokens and test line ends for trailing blanks; building it costs ~19 instructions per 16 input bytes for
+// ALL bytes, while only the ~40 header bytes of a record are ever searched.  Here the record thread scans its
+// own header with the same SWAR test, 4 bytes per shared-memory load.
+
+// first position in [p, e) holding whitespace (Python-2 str set), e if none
+__device__ __forceinline__ uint32_t f6_find_ws(const F2Tile &t, uint32_t p, uint32_t e)
+{
+    if (p >= e) return e;
+    if (p >= t.tbase && e - t.tbase <= t.win) {                 // the whole range is staged
+        const uint32_t a = t.sdata + (p - t.tbase), end = t.sdata + (e - t.tbase);
+        uint32_t a4 = a & ~3u;
+        uint32_t w = lds32(a4);
+        uint32_t f = f2_c_flags(w) & (0xffffffffu << ((a & 3u) * 8u));   // bytes <= 0x20 at or after a
+        for (;;) {
+            while (f) {
+                const uint32_t i = ((uint32_t)__ffs((int)f) - 1u) >> 3;
+                const uint32_t at = a4 + i;
+                if (at >= end) return e;
+                if (is_ws((w >> (8u * i)) & 0xffu)) return p + (at - a);
+                f &= f - 1u;                                    // a control character inside the token
+            }
+            a4 += 4u;
+            if (a4 >= end) return e;
+            w = lds32(a4);
+            f = f2_c_flags(w);
+        }
+    }
+    for (; p < e; ++p)
+        if (is_ws(f2_byte(t, p))) return p;
+    return e;
+}
+
+__device__ __forceinline__ uint32_t f6_rstrip(const F2Tile &t, uint32_t s, uint32_t e)
+{
+    while (e > s && is_ws(f2_byte(t, e - 1u))) --e;
+    return e;
+}
+
+// f2_parse without t.bc (FastqReader.py:37-44, FastqSeq.py:55)
+__device__ __forceinline__ F2Rec f6_parse(const F2Tile &t, uint32_t hs, const uint16_t *pos, uint32_t li, uint32_t npos)
+{
+    F2Rec r;
+    r.complete = r.valid = false;
+    r.name_off = r.nlen = r.seq_off = r.qual_off = r.seq_len = r.end = 0u;
+    if (hs > t.n) return r;
+    const uint32_t nl0 = li < npos ? t.tbase + pos[li] : f2_next_nl(t, hs);
+    if (nl0 == F2_NONE || nl0 >= t.n) return r;           // a line ending at n is the file's last line
+    const uint32_t nl1 = li + 1u < npos ? t.tbase + pos[li + 1u] : f2_next_nl(t, nl0 + 1u);
+    if (nl1 == F2_NONE || nl1 >= t.n) return r;
+    const uint32_t nl2 = li + 2u < npos ? t.tbase + pos[li + 2u] : f2_next_nl(t, nl1 + 1u);
+    if (nl2 == F2_NONE || nl2 >= t.n) return r;
+    const uint32_t nl3 = li + 3u < npos ? t.tbase + pos[li + 3u] : f2_next_nl(t, nl2 + 1u);
+    if (nl3 == F2_NONE) return r;
+    r.complete = true;
+    r.end = nl3 < t.n ? nl3 + 1u : t.n;
+    // name = line.rstrip()[1:].split()[0]: drop the first byte whatever it is, skip blanks, take the token
+    uint32_t p = hs + 1u;
+    while (p < nl0 && is_ws(f2_byte(t, p))) ++p;
+    r.name_off = p < nl0 ? p : nl0;
+    r.nlen = p < nl0 ? f6_find_ws(t, p, nl0) - p : 0u;
+    r.seq_off = nl0 + 1u;
+    r.qual_off = nl2 + 1u;
+    r.seq_len = f6_rstrip(t, r.seq_off, nl1) - r.seq_off;
+    r.valid = r.seq_len == f6_rstrip(t, r.qual_off, nl3) - r.qual_off;
+    return r;
+}
+
 template <bool REDO>
 __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ BatchDev b, uint32_t total_tiles)
 {
@@ -32,7 +101,6 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t sm0 = smem_u32(f6_smem);
     const u64 *s_bm = reinterpret_cast<const u64 *>(f6_smem + F3_OFF_BM);
-    const u64 *s_bc = reinterpret_cast<const u64 *>(f6_smem + F3_OFF_BC);
     uint16_t *s_pos = reinterpret_cast<uint16_t *>(f6_smem + F3_OFF_POS);
     uint32_t *s_misc = reinterpret_cast<uint32_t *>(f6_smem + F3_OFF_MISC);
     const uint32_t s_bar = sm0 + F3_OFF_MISC + 64, a_pos = sm0 + F3_OFF_POS;
@@ -99,7 +167,7 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
         T.data = st.data;
         T.sdata = sm0;
         T.bm = s_bm;
-        T.bc = s_bc;
+        T.bc = nullptr;                                         // no candidate bitmap here: f6_parse
         T.tbase = lt * (uint32_t)F2_TILE;
         T.cap = (uint32_t)F2_WIN;
         T.n = st.n;
@@ -122,15 +190,12 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
                 if (i == 4 && tid >= F2_HALO / 16) break;       // halo: 128 chunks, warps 0-3
                 const uint4 q = lds128(sm0 + off);
                 uint32_t m = f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w));
-                uint32_t cd = f2_gather16(f2_c_flags(q.x), f2_c_flags(q.y), f2_c_flags(q.z), f2_c_flags(q.w));
                 if (edge) {
                     const uint32_t keep = off >= T.win ? 0u : (T.win - off >= 16u ? 0xffffu : (1u << (T.win - off)) - 1u);
                     m &= keep;
-                    cd &= keep;
                     if ((vbit >> 4) == c && f2_byte(T, T.n - 1u) != '\n') m |= 1u << (vbit & 15u);   // no final '\n'
                 }
                 sts16(sm0 + F3_OFF_BM + 2u * c, m);
-                sts16(sm0 + F3_OFF_BC + 2u * c, cd);
             }
         }
         __syncthreads();                                        // B1: bitmaps complete
@@ -232,9 +297,9 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
 
         // record of slot i (FastqReader.py:37-44); false: only the redo pass can find it (line-end list overflow)
         auto parse_slot = [&](uint32_t slot, F2Rec &R) -> bool {
-            if (first && slot == 0u) { R = f2_parse(T, 0u, s_pos, 0u, npos); return true; }
+            if (first && slot == 0u) { R = f6_parse(T, 0u, s_pos, 0u, npos); return true; }
             const uint32_t ti = t0 + 4u * (slot - first);
-            if (ti < npos) { R = f2_parse(T, T.tbase + s_pos[ti] + 1u, s_pos, ti + 1u, npos); return true; }
+            if (ti < npos) { R = f6_parse(T, T.tbase + s_pos[ti] + 1u, s_pos, ti + 1u, npos); return true; }
             R.complete = R.valid = false;
             R.name_off = R.nlen = R.seq_off = R.qual_off = R.seq_len = R.end = 0u;
             if (!REDO) return false;
@@ -246,7 +311,7 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
                 ppos = e + 1u;
                 ++k;
             }
-            if (e != F2_NONE) R = f2_parse(T, e + 1u, s_pos, 0u, 0u);
+            if (e != F2_NONE) R = f6_parse(T, e + 1u, s_pos, 0u, 0u);
             return true;
         };
         // redo pass: outputs at the raw record index, as k_frame2.  First pass: the same fields at scratch position
