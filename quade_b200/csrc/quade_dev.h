@@ -22,6 +22,8 @@ namespace quade {
 
 constexpr int kMaxStreams = 4;
 constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
+constexpr int kTileChunk = 1024;   // k_frame6 / k_tilescan: tiles per chunk of the tile table (16 MiB of input)
+constexpr int kMaxChunks = 256;    // >= kMaxStreamBytes / (16 KiB * kTileChunk)
 
 // device-resident scalars of one batch; copied back to the host as a whole
 struct BatchState {
@@ -40,6 +42,7 @@ struct BatchState {
     uint32_t compact_tp;               // pairs per k_compact3 tile, from the mean record size (k_pairing)
     uint32_t scratch_cursor[kMaxStreams]; // k_frame6: records reserved in the per-stream scratch arrays
     uint32_t n_redo, ticket_redo;      // k_frame6: tiles whose guessed record phase was wrong (malformed text)
+    uint32_t chunk_lines[kMaxStreams][kMaxChunks]; // k_frame6: line ends per chunk of kTileChunk tiles
     unsigned long long out_total[2];   // bytes of the R1 / R2 arenas
 };
 

@@ -246,6 +246,7 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
                 if ((u64)sb + nres > (u64)st.cap_rec || total + s_misc[8] > (uint32_t)F3_PCAP) sb = F2_NONE;   // -> redo
                 s_misc[9] = sb;
             }
+            if (!REDO) atomicAdd(&S->chunk_lines[s][lt / (uint32_t)kTileChunk], total);   // for k_tilescan
             ticket_next();
         }
 
@@ -367,22 +368,32 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// k_tilescan: one CTA per stream.  tile_tab[t] = {line ends, guessed t0, records, scratch base} becomes
-// {k0, ok, records, scratch base}; n_lines; tiles to parse again are appended to the redo list.
+// k_tilescan: one CTA per chunk of kTileChunk tiles of one stream, one tile per thread.  The line ends of the
+// chunks before it were summed by k_frame6 (chunk_lines), so every CTA is independent.
+// tile_tab[t] = {line ends, guessed t0, records, scratch base} becomes {k0, ok, records, scratch base}; n_lines;
+// tiles to parse again are appended to the redo list.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024) k_tilescan(const __grid_constant__ BatchDev b)
+__global__ void __launch_bounds__(kTileChunk) k_tilescan(const __grid_constant__ BatchDev b)
 {
     __shared__ uint32_t s_warp[33];
-    const int s = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ uint32_t s_base;
+    const int s = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const StreamDev &st = b.st[s];
     BatchState *S = b.state;
-    const uint32_t n_t = st.n ? st.n / (uint32_t)F2_TILE + 1u : 0u;
-    const uint32_t run = (n_t + 1023u) / 1024u;
-    const uint32_t t_lo = min(n_t, (uint32_t)tid * run), t_hi = min(n_t, t_lo + run);
-    uint32_t sum = 0;
-#pragma unroll 8
-    for (uint32_t t = t_lo; t < t_hi; ++t) sum += st.tile_tab[t].x;             // independent loads: 8 in flight
-    uint32_t inc = sum;
+    const uint32_t n_t = st.n ? st.n / (uint32_t)F2_TILE + 1u : 0u, chunk = blockIdx.x;
+    if (chunk * (uint32_t)kTileChunk >= n_t) return;
+    if (tid == 0) s_base = 0u;
+    __syncthreads();
+    {                                                           // line ends in the chunks before this one
+        uint32_t v = (uint32_t)tid < chunk && tid < kMaxChunks ? S->chunk_lines[s][tid] : 0u;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0 && v) atomicAdd(&s_base, v);
+    }
+    const uint32_t t = chunk * (uint32_t)kTileChunk + (uint32_t)tid;
+    const uint4 e = t < n_t ? st.tile_tab[t] : make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t total = e.x;
+    uint32_t inc = total;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
@@ -399,31 +410,18 @@ __global__ void __launch_bounds__(1024) k_tilescan(const __grid_constant__ Batch
             if (lane >= o) wi += x;
         }
         s_warp[lane] = wi - w;
-        if (lane == 31) s_warp[32] = wi;
     }
     __syncthreads();
-    uint32_t k0 = s_warp[warp] + inc - sum;
-    if (tid == 0) S->n_lines[s] = s_warp[32];
-    for (uint32_t tb = t_lo; tb < t_hi; tb += 8u) {            // 8 entries loaded at once, then stored
-        uint4 ev[8];
-#pragma unroll
-        for (uint32_t q = 0; q < 8; ++q) ev[q] = tb + q < t_hi ? st.tile_tab[tb + q] : make_uint4(0u, 0u, 0u, 0u);
-#pragma unroll
-        for (uint32_t q = 0; q < 8; ++q) {
-            const uint32_t t = tb + q;
-            if (t >= t_hi) break;
-            const uint4 e = ev[q];
-            const uint32_t total = e.x, first = t == 0u ? 1u : 0u;
-            const uint32_t nslot = ((k0 + total) >> 2) - (k0 >> 2) + first;
-            const bool ok = nslot == 0u || (e.y == ((3u - k0) & 3u) && e.w != F2_NONE);
-            st.tile_tab[t] = make_uint4(k0, ok ? 1u : 0u, nslot, e.w);
-            if (!ok) {
-                const uint32_t idx = atomicAdd(&S->n_redo, 1u);
-                if (idx < b.redo_cap) b.redo_list[idx] = (uint32_t)s << 28 | t;
-            }
-            k0 += total;
-        }
+    if (t >= n_t) return;
+    const uint32_t k0 = s_base + s_warp[warp] + inc - total, first = t == 0u ? 1u : 0u;
+    const uint32_t nslot = ((k0 + total) >> 2) - (k0 >> 2) + first;
+    const bool ok = nslot == 0u || (e.y == ((3u - k0) & 3u) && e.w != F2_NONE);
+    st.tile_tab[t] = make_uint4(k0, ok ? 1u : 0u, nslot, e.w);
+    if (!ok) {
+        const uint32_t idx = atomicAdd(&S->n_redo, 1u);
+        if (idx < b.redo_cap) b.redo_list[idx] = (uint32_t)s << 28 | t;
     }
+    if (t == n_t - 1u) S->n_lines[s] = k0 + total;
 }
 
 // ------------------------------------------------------------------------------------------------------------

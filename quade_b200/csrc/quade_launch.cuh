@@ -10,7 +10,7 @@ void set_compact_variant(int v) { g_compact_variant = v; }
 static int g_frame_variant = 10, g_occ_frame2 = 0, g_occ_frame3 = 0;  // 10 = k_frame6 (default); 2..9: earlier single-pass variants
 void set_frame_variant(int v) { g_frame_variant = v; }
 int frame_variant() { return g_frame_variant; }
-int frame_launches() { return g_frame_variant == 10 ? 4 : 1; }
+int frame_launches() { return g_frame_variant == 10 ? 4 : 1; }   // k_frame6, k_tilescan, k_densify, k_frame6<redo>
 
 static void init_launch_config()
 {
@@ -82,9 +82,6 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
         uint32_t g6 = (uint32_t)(g_sms * occ6);
         if (g6 > total) g6 = total;
         k_frame6<false><<<g6, F6T, F3_SMEM, s>>>(b, total);
-        k_tilescan<<<b.n_streams, 1024, 0, s>>>(b);
-        k_densify<<<(uint32_t)g_sms * 4u, 256, 0, s>>>(b, total);
-        k_frame6<true><<<(uint32_t)g_sms, F6T, F3_SMEM, s>>>(b, total);
         return;
     }
     if (g_frame_variant >= 7 && g_frame_variant <= 9) {        // k_frame5: scan / look-back / parse warps
@@ -149,6 +146,16 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
 void launch_fix(const BatchDev &b, cudaStream_t s)
 {
     init_launch_config();
+    if (g_frame_variant == 10) {                               // the second half of the k_frame6 pipeline
+        const uint32_t total = b.frame_tile_start[b.n_streams];
+        if (total) {
+            uint32_t max_tiles = 0;
+            for (int i = 0; i < b.n_streams; ++i) max_tiles = max(max_tiles, b.st[i].n ? b.st[i].n / (uint32_t)F2_TILE + 1u : 0u);
+            k_tilescan<<<dim3((max_tiles + kTileChunk - 1) / kTileChunk, b.n_streams), kTileChunk, 0, s>>>(b);
+            k_densify<<<(uint32_t)g_sms * 4u, 256, 0, s>>>(b, total);
+            k_frame6<true><<<(uint32_t)g_sms, F6T, F3_SMEM, s>>>(b, total);
+        }
+    }
     const uint32_t gx = (uint32_t)max(1, g_sms * 4 / b.n_streams);
     k_fix_compact<<<dim3(gx, b.n_streams), 256, 0, s>>>(b);
     k_fix_copyback<<<dim3(gx, b.n_streams), 256, 0, s>>>(b);
