@@ -44,7 +44,21 @@ def parse_args():
     ap.add_argument("--cpu-pairs", type=int, default=1_000_000, help="sample size of the CPU baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--slots", type=int, default=3, help="batch slots in flight (submit/collect ring)")
+    ap.add_argument("--spinup-ms", type=float, default=400.0,
+                    help="untimed extra warm-up before the W warm-up steps: the GPU sits idle while the inputs are generated "
+                         "on the host and needs tens of ms of load to be back at full clocks")
     return ap.parse_args()
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full summary
+    of this same command (profiles/r01_traffic.json, written by tools/ncu_traffic.py); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as fh:
+            return json.load(fh)["kernels"][kernel]["dram_bytes_per_launch"]
+    except Exception:
+        return None
 
 
 def peaks():
@@ -56,36 +70,50 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """nvidia-smi clocks / throttle reasons during the timed region.  ONE long-running `nvidia-smi -lms` process,
+    started before the big pinned allocations: forking this process once it maps gigabytes of pinned memory takes
+    milliseconds with the GIL held, which stalled the submit loop inside the timed region (2.0 -> 2.3-3.6 ms per
+    step when the sampler forked per sample)."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.rows, self.t0, self.t1 = [], None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "25"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+        self.start()
 
     def run(self):
-        while not self._stop_evt.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [x.strip() for x in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.rows.append(parts)
-            except Exception:
-                pass
-            self._stop_evt.wait(0.1)
+        if self.proc is None:
+            return
+        for line in self.proc.stdout:                      # blocking read: releases the GIL
+            parts = [x.strip() for x in line.strip().split(",")]
+            if len(parts) >= 6:
+                self.rows.append((time.time(), parts))
+
+    def begin(self):
+        self.t0 = time.time()
 
     def stop(self):
-        self._stop_evt.set()
-        self.join(timeout=6)
-        if not self.rows:
+        self.t1 = time.time()
+        time.sleep(0.06)                                   # one more sample after the region
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=3)
+        rows = [p for (t, p) in self.rows if self.t0 is not None and self.t0 <= t <= self.t1 + 0.05]
+        if not rows and self.rows:                         # region shorter than the sampling period: nearest sample
+            rows = [min(self.rows, key=lambda tp: abs(tp[0] - self.t1))[1]]
+        if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
-        sm = sorted(float(r[0]) for r in self.rows)
+        sm = sorted(float(r[0]) for r in rows)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows)}
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons, "samples": len(rows)}
 
 
 class CpuLeg:
@@ -148,6 +176,7 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    sampler = ClockSampler(local_rank)                 # forked now, while this process is still small
     synth = Synth.from_config(args.config)
     min_qual = synth.min_qual if args.min_qual is None else args.min_qual
     P, ns = args.pairs, synth.n_streams
@@ -161,7 +190,7 @@ def run_ours(args, rank, world, local_rank):
     for t, b in zip(dev_in, pinned):
         t[:b.nbytes].copy_(torch.from_numpy(b.array), non_blocking=False)
     ctx = DemuxContext(synth.dual, synth.spans(), min_qual, synth.sample_keys(), device=local_rank,
-                       max_stream_bytes=max(sizes) + 4096, max_pairs=P + 1024, n_slots=2)
+                       max_stream_bytes=max(sizes) + 4096, max_pairs=P + 1024, n_slots=args.slots)
     stream = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
     ptrs = [t.data_ptr() for t in dev_in]
 
@@ -174,7 +203,7 @@ def run_ours(args, rank, world, local_rank):
         """n batches back to back, two in flight; returns the collected results."""
         res = []
         for i in range(n):
-            if ctx.in_flight == 2:
+            if ctx.in_flight == args.slots:
                 res.append(ctx.collect())
             ctx.submit_device(ptrs, sizes, last=True, ticket=i)
         while ctx.in_flight:
@@ -182,10 +211,12 @@ def run_ours(args, rank, world, local_rank):
         return res
 
     # ---- value: HBM-resident inputs, kernels only --------------------------------------------------------
+    t_spin = time.perf_counter()
+    while (time.perf_counter() - t_spin) * 1e3 < args.spinup_ms:
+        device_steps(4)
     device_steps(args.warmup)
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.begin()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     results = device_steps(args.steps)
@@ -214,7 +245,7 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_src = peaks()
     ach = alg[dom] / (kms[dom] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "k_" + dom, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom],
+                "traffic": ncu_traffic("k_" + dom), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom],
                 "ms_per_launch": kms[dom],
                 "per_kernel": {k: {"ms": kms[k], "GB/s": (alg[k] / (kms[k] * 1e-3) / 1e9) if k in alg else None} for k in kms},
                 "pipeline": {"algorithmic_bytes_per_step": in_bytes + out_bytes,
@@ -229,7 +260,7 @@ def run_ours(args, rank, world, local_rank):
         def host_steps(n):
             done = 0
             for i in range(n):
-                if ctx.in_flight == 2:
+                if ctx.in_flight == args.slots:
                     r = ctx.collect()
                     done += int(r.arena(0)[-1]) * 0 + r.n_pairs      # touches the copied-back result
                 ctx.submit(host, last=True, ticket=i)
@@ -237,7 +268,7 @@ def run_ours(args, rank, world, local_rank):
                 r = ctx.collect()
                 done += int(r.arena(1)[-1]) * 0 + r.n_pairs
             return done
-        host_steps(max(2, min(args.warmup, 3)))
+        host_steps(max(args.slots + 1, args.warmup))       # every slot's pinned output arena exists before timing
         barrier()
         t0 = time.perf_counter()
         done = host_steps(args.steps)

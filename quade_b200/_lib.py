@@ -8,7 +8,8 @@ from . import build as _build
 QUADE_OK = 0
 ERR_BLANK_HEADER, ERR_NOMEM, ERR_BAD_SAMPLE, ERR_CUDA, ERR_ARG, ERR_CAPACITY, ERR_UNSUPPORTED, ERR_STATE = range(-1, -9, -1)
 BATCH_LAST, BATCH_DEVICE = 1, 2
-K_NAMES = ["frame", "validate", "pairing", "classify", "binscan", "offsets", "compact"]
+# stage 1 (QUADE_K_VALIDATE in the header) = k_tilescan + k_densify + redo pass + k_fix_* of the k_frame6 pipeline
+K_NAMES = ["frame", "densify", "pairing", "classify", "binscan", "offsets", "compact"]
 K_COUNT = len(K_NAMES)
 SYMBOLS = ["quade_version", "quade_last_error", "quade_device_count", "quade_host_alloc", "quade_host_free",
            "quade_ctx_create", "quade_ctx_destroy", "quade_ctx_set_samples", "quade_submit", "quade_collect",

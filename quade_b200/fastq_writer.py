@@ -2,7 +2,7 @@
 
 The reference appends ":INDEX[:MOLECULAR]" to both read names, serialises the pair with FastqSeq.fastqstr and
 buffers 20 records before appending a gzip member (FastqWriter.py:48-74).  Here the suffix and the serialisation
-are done by k_compact on the GPU; a writer receives the already serialised R1 / R2 byte ranges of its bin for one
+are done by k_compact3 on the GPU; a writer receives the already serialised R1 / R2 byte ranges of its bin for one
 batch and keeps only the reference's host duties: lazy creation of `<name>_R1.fastq.gz` / `<name>_R2.fastq.gz` in
 the current working directory on the first record (:55-57, :76-81) and appending gzip members in arrival order
 (:83-90).  Parity is on the decompressed stream (gzip members carry mtime).

@@ -2,7 +2,7 @@
 
 The reference's `FastqReader(path)` (src/pyFastq/FastqReader.py:25-58) is a generator that frames 4 lines per
 record and builds one FastqSeq per record on the CPU.  Here the framing, validation and slicing run on the GPU
-(k_frame / k_classify), so `FastqReader(path)` only does what is left for the host: open the file with the
+(k_frame6 / k_classify2), so `FastqReader(path)` only does what is left for the host: open the file with the
 reference's rule (gzip iff the path ends in "gz", FastqReader.py:30) and move raw bytes into page-locked
 buffers that `quade_submit` copies to the device.  There is no per-record Python code and no CPU parser.
 """

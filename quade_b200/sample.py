@@ -1,7 +1,7 @@
 """Sample: the reference's class-level sample registry, counters and report (src/Sample.py:19-175).
 
 Same class fields and methods.  The per-pair classification of `Sample.FINDER` (Sample.py:56-91: dict lookup of
-the upper-cased fused index, min(phred) >= MIN_QUAL, counters, writer dispatch) runs on the GPU in k_classify; here
+the upper-cased fused index, min(phred) >= MIN_QUAL, counters, writer dispatch) runs on the GPU in k_classify2; here
 FINDER takes one collected batch (a DemuxResult) and applies what the kernels decided: it adds the per-bin pair
 counts to the class and sample counters and hands every non-empty bin range to that bin's FastqWriter.
 """

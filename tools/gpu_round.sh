@@ -13,6 +13,6 @@ python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${t
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_ncu1.log 2>&1
 echo "ncu launches exit $?"
-ncu --set full --clock-control none --import-source on -k regex:'k_frame2|k_compact3|k_classify2' -s 9 -c 3 \
+ncu --set full --clock-control none --import-source on -k regex:'k_frame6|k_compact3|k_classify2|k_densify|k_tilescan|k_offsets|k_binscan_blocks' -s 24 -c 8 \
     -f -o gpurun_out/${tag}_prof python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_ncu2.log 2>&1
 echo "ncu full exit $?"
