@@ -73,7 +73,8 @@ class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons during the timed region.  ONE long-running `nvidia-smi -lms` process,
     started before the big pinned allocations: forking this process once it maps gigabytes of pinned memory takes
     milliseconds with the GIL held, which stalled the submit loop inside the timed region (2.0 -> 2.3-3.6 ms per
-    step when the sampler forked per sample)."""
+    step when the sampler forked per sample).  Period 100 ms: at 25 ms the driver queries themselves delayed kernel
+    launches (2 of 6 runs +18 %); a region shorter than the period reports the nearest sample."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -82,7 +83,7 @@ class ClockSampler(threading.Thread):
         self.rows, self.t0, self.t1 = [], None, None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "25"],
+                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("QUADE_BENCH_SMI_MS", "100")],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             self.proc = None

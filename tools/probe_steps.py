@@ -3,7 +3,8 @@ sys.path.insert(0, "/root/repo")
 import numpy as np, torch
 from quade_b200 import DemuxContext, PinnedBuffer
 from quade_b200.synth import Synth
-s = Synth.from_config("cfg3"); P = 2_000_000
+import os
+s = Synth.from_config(os.environ.get("QUADE_CFG", "cfg3")); P = 2_000_000
 sizes = s.sizes(0, P)
 host = [np.empty(n, dtype=np.uint8) for n in sizes]
 s.fill(0, P, host, n_threads=16)
@@ -17,7 +18,7 @@ for rep in range(3):
     for i in range(8):
         if ctx.in_flight == 2:
             a = time.perf_counter(); r = ctx.collect(); tc.append(time.perf_counter() - a)
-        a = time.perf_counter(); ctx.submit_device(ptrs, sizes, last=True, ticket=i); ts.append(time.perf_counter() - a)
+        a = time.perf_counter(); ctx.submit_device(ptrs[:len(sizes)], sizes, last=True, ticket=i); ts.append(time.perf_counter() - a)
     while ctx.in_flight:
         a = time.perf_counter(); r = ctx.collect(); tc.append(time.perf_counter() - a)
     torch.cuda.synchronize(); dt = time.perf_counter() - t0
