@@ -76,6 +76,7 @@ __device__ __forceinline__ void emit_generic(const BatchDev &b, int k, uint32_t 
 struct TileMeta {
     uint4 rc;          // this lane's record {name_off, seq_off, qual_off, seq_len}
     uint32_t nlen, cls, ooff;
+    uint4 suf0, suf1;             // first two 16-byte vectors of the pair's suffix (R1 lanes of role 0)
     uint32_t start0, start1, size0, size1;   // staged span per stream (uniform); size 0 = nothing staged
     bool staged;                  // uniform: the spans fit the stage
 };
@@ -109,17 +110,29 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
     const bool rec_lane = r < 2u * tp;
     const uint32_t sufv = b.suf_cap >> 4;                              // suffix slot = sufv 16-byte vectors
 
-    auto load_meta = [&](uint32_t tile, TileMeta &m) {
+    // per-pair metadata of a tile.  load_raw only ISSUES the global loads (nothing consumes them), so that the
+    // loads of the next tile fly during this tile's phases; finish_meta turns them into the staged spans.
+    auto load_raw = [&](uint32_t tile, TileMeta &m) {
         const uint32_t p = tile * tp + pr;
         m.rc = make_uint4(0, 0, 0, 0);
         m.nlen = m.cls = m.ooff = 0u;
+        m.suf0 = m.suf1 = make_uint4(0, 0, 0, 0);
         if (rec_lane && tile < n_tiles && p < n_pairs) {
             m.cls = b.cls[p];
-            if (m.cls >> 31) {
-                m.rc = b.st[k].rec[p];
-                m.nlen = b.st[k].vnlen[p];
-                m.ooff = k ? b.out2[p] : b.out1[p];
+            m.rc = b.st[k].rec[p];
+            m.nlen = b.st[k].vnlen[p];
+            m.ooff = k ? b.out2[p] : b.out1[p];
+            if (role == 0u && k == 0u) {                                // the pair's suffix, staged by this lane
+                const uint4 *sp = reinterpret_cast<const uint4 *>(b.suffix + (size_t)p * b.suf_cap);
+                m.suf0 = sp[0];
+                if (sufv > 1u) m.suf1 = sp[1];
             }
+        }
+    };
+    auto finish_meta = [&](TileMeta &m) {
+        if (!(m.cls >> 31)) {                                           // the bin's writer is off: nothing to emit
+            m.rc = make_uint4(0, 0, 0, 0);
+            m.nlen = m.ooff = 0u;
         }
         // span of each stream: first .. last written record of the tile (lanes of role 0 vote)
         m.staged = true;
@@ -158,16 +171,18 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
     uint32_t tile = blockIdx.x, it = 0;
     TileMeta cur, nxt;
     if (tile < n_tiles) {
-        load_meta(tile, cur);
+        load_raw(tile, cur);
+        finish_meta(cur);
         issue(cur, 0);
     }
 #pragma unroll 1
     for (; tile < n_tiles; tile += gridDim.x, ++it) {
         const uint32_t stage = C3_STAGES == 2 ? (it & 1u) : 0u;
         const uint32_t ntile = tile + gridDim.x;
-        if (ntile < n_tiles) {
-            load_meta(ntile, nxt);
-            if (C3_STAGES == 2) issue(nxt, stage ^ 1u);
+        load_raw(ntile, nxt);                                          // loads only; consumed at the end of the iteration
+        if (C3_STAGES == 2 && ntile < n_tiles) {
+            finish_meta(nxt);
+            issue(nxt, stage ^ 1u);
         }
         if (cur.size0 | cur.size1) {
             const uint32_t bar = s_bar + 8u * stage;
@@ -195,8 +210,10 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
         if (fast) fast = lds8(sbase + cur.rc.y + L + 1u) == '+' && lds8(sbase + cur.rc.z + L) == '\n';
         // stage the pair's suffix (one copy per pair, by the R1 lanes of role 0)
         if (role == 0u && k == 0u && written) {
+            sts128(s_suf + (pr * C3_SUFV + 0u) * 16u, cur.suf0);    // prefetched with the tile's metadata
+            sts128(s_suf + (pr * C3_SUFV + 1u) * 16u, cur.suf1);
             const uint4 *sp = reinterpret_cast<const uint4 *>(b.suffix + (size_t)p * b.suf_cap);
-            for (uint32_t v = 0; v < sufv && v < (uint32_t)C3_SUFV; ++v) sts128(s_suf + (pr * C3_SUFV + v) * 16u, sp[v]);
+            for (uint32_t v = 2; v < sufv && v < (uint32_t)C3_SUFV; ++v) sts128(s_suf + (pr * C3_SUFV + v) * 16u, sp[v]);
         }
         __syncwarp();
         if (fast) {
@@ -259,7 +276,10 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
             }
         }
         __syncwarp();
-        if (C3_STAGES == 1 && ntile < n_tiles) issue(nxt, 0u);
+        if (C3_STAGES == 1) {
+            finish_meta(nxt);
+            if (ntile < n_tiles) issue(nxt, 0u);
+        }
         cur = nxt;
     }
 }
