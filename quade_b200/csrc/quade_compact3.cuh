@@ -26,7 +26,7 @@ constexpr int C3_HS = 176;                // HEAD slot stride: 16-byte multiple 
 constexpr int C3_SUFV = 4;                // staged suffix: up to 64 bytes per pair
 constexpr int C3_STAGES = 1;               // 1: more resident warps hide the copy latency; 2: per-warp prefetch
 constexpr int C3_IN_BYTES = C3_STAGES * 2 * (C3_CAP + 32);
-constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * 16 + 32;
+constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * 32 + 32;
 
 // shared -> shared copy of n bytes, any alignment on both sides, full destination words by funnel shift
 __device__ __forceinline__ void seg_copy(uint32_t dst, uint32_t src, uint32_t n)
@@ -96,8 +96,8 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
     const uint32_t s_in = sm0;                                         // [stage][stream][C3_CAP + 32]
     const uint32_t s_head = s_in + C3_IN_BYTES;                        // [2*TP][C3_HS]
     const uint32_t s_suf = s_head + 2 * C3_TP * C3_HS;                 // [TP][64]
-    const uint32_t s_par = s_suf + C3_TP * C3_SUFV * 16;               // [2*TP] uint4
-    const uint32_t s_bar = s_par + 2 * C3_TP * 16;                     // 2 mbarriers
+    const uint32_t s_par = s_suf + C3_TP * C3_SUFV * 16;               // [2*TP] 2 x uint4: phase-2 parameters
+    const uint32_t s_bar = s_par + 2 * C3_TP * 32;                     // 2 mbarriers
     if (lane == 0) {
         mbar_init(s_bar, 1);
         mbar_init(s_bar + 8, 1);
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
         const uint32_t srcb = sbase + cur.rc.y - D1 - a;
         const uint32_t hb = s_head + r * C3_HS + (srcb & 15u);
         bool fast = written && cur.staged && (cur.rc.z - cur.rc.y == L + 3u) && (15u + a + J <= (uint32_t)C3_HS) &&
-                    total < (1u << 20) && suf_len <= (sufv < (uint32_t)C3_SUFV ? sufv : (uint32_t)C3_SUFV) * 16u && (cur.rc.z + L < b.st[k].n);
+                    total < (1u << 20) - 16u && suf_len <= (sufv < (uint32_t)C3_SUFV ? sufv : (uint32_t)C3_SUFV) * 16u && (cur.rc.z + L < b.st[k].n);
         if (fast) fast = lds8(sbase + cur.rc.y + L + 1u) == '+' && lds8(sbase + cur.rc.z + L) == '\n';
         // stage the pair's suffix (one copy per pair, by the R1 lanes of role 0)
         if (role == 0u && k == 0u && written) {
@@ -228,9 +228,21 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
             seg_copy(d1, s1, n1);
             seg_copy(d2, s2, n2);
         }
+        // everything phase 2 needs per record is derived HERE, once, by the record's lane (phase 2 runs these
+        // values through all 32 lanes 2*tp times per tile): destination pointer of the record's first 16-byte
+        // frame, number of full vectors, byte ranges of the partial first / last vector, source addresses
         if (role == 0u && rec_lane) {
-            const uint32_t flags = (written ? 1u : 0u) | (fast ? 2u : 0u);
-            sts128(s_par + r * 16u, fast ? make_uint4(cur.ooff, total | J << 20, srcb, flags) : make_uint4(cur.ooff, 0u, s_in, flags));
+            if (fast) {
+                const uint32_t endb = a + total, F1 = endb >> 4;
+                const u64 gp = (u64)(uintptr_t)(b.out[k] + (size_t)(cur.ooff - a));
+                const uint32_t h0 = a, h1 = a ? (endb < 16u ? endb : 16u) : 0u;     // first partial vector [h0, h1)
+                const uint32_t t1 = (F1 > 0u || a == 0u) ? endb : 0u;               // last partial vector [16 F1, t1)
+                sts128(s_par + r * 32u, make_uint4((uint32_t)gp, (uint32_t)(gp >> 32), F1 | (a ? 1u : 0u) << 16, a + J));
+                sts128(s_par + r * 32u + 16u, make_uint4(hb, srcb, (srcb & 15u) | h0 << 8 | h1 << 16, t1));
+            } else {
+                sts128(s_par + r * 32u, make_uint4(cur.ooff, 0u, 0u, 0u));          // inactive in phase 2
+                sts128(s_par + r * 32u + 16u, make_uint4(s_in, s_in, 0u, 0u));
+            }
         }
         const unsigned slow = __ballot_sync(0xffffffffu, role == 0u && written && !fast);
         __syncwarp();
@@ -239,40 +251,35 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
         const uint32_t nrec = 2u * tp;
 #pragma unroll 2
         for (uint32_t i = 0; i < nrec; ++i) {
-            const uint4 P = lds128(s_par + i * 16u);
-            const bool act = (P.w & 3u) == 3u;
-            const uint32_t kk = i >= tp ? 1u : 0u;
-            const uint32_t tot = P.y & 0xfffffu, Ji = P.y >> 20, ai = P.x & 15u;
-            uint8_t *gdst = b.out[kk] + (size_t)(P.x - ai);
-            const uint32_t endb = ai + tot, F1 = endb >> 4, hend = ai + Ji;      // hend: end of the HEAD part
-            const uint32_t sb = P.z, sr = sb & 15u;
-            const uint32_t hbi = s_head + i * C3_HS + sr;
+            const uint4 A = lds128(s_par + i * 32u), B = lds128(s_par + i * 32u + 16u);
+            uint8_t *gdst = reinterpret_cast<uint8_t *>((uintptr_t)((u64)A.y << 32 | A.x));
+            const uint32_t F1 = A.z & 0xffffu, vlo = A.z >> 16, hend = A.w;        // hend: end of the HEAD part
+            const uint32_t hbi = B.x, sb = B.y, sr = B.z & 0xffu, h0 = (B.z >> 8) & 0xffu, h1 = B.z >> 16, t1 = B.w;
             {
                 const uint32_t v = lane, y0 = 16u * v;
                 const uint32_t sa = ((y0 < hend ? hbi : sb) + y0) & ~15u;
                 const uint4 val = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
-                if (act && v < F1 && (v > 0u || ai == 0u)) *reinterpret_cast<uint4 *>(gdst + y0) = val;
+                if (v >= vlo && v < F1) *reinterpret_cast<uint4 *>(gdst + y0) = val;
             }
-            if (F1 > 32u && act) {                                                 // records longer than 512 bytes
+            if (F1 > 32u) {                                                        // records longer than 512 bytes
 #pragma unroll 1
                 for (uint32_t v = lane + 32u; v < F1; v += 32) {
                     const uint32_t sa = (sb + 16u * v) & ~15u;
                     *reinterpret_cast<uint4 *>(gdst + 16u * v) = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
                 }
             }
-            // first partial vector: bytes [ai, min(16, endb)) by lanes 0-15; last one: [16*F1, endb) by lanes 16-31
+            // first partial vector: bytes [h0, h1) by lanes 0-15; last one: [16*F1, t1) by lanes 16-31
             const uint32_t y = lane < 16 ? (uint32_t)lane : 16u * F1 + (uint32_t)(lane - 16);
-            const bool okb = act && y < endb && (lane < 16 ? (ai != 0u && y >= ai) : (F1 > 0u || ai == 0u));
+            const bool okb = lane < 16 ? (y >= h0 && y < h1) : y < t1;
             const uint32_t bsrc = (y < hend ? hbi : sb) + y;
             if (okb) gdst[y] = (uint8_t)lds8(bsrc);
         }
         if (slow) {                                                                // records off the fast path
 #pragma unroll 1
-            for (uint32_t i = 0; i < nrec; ++i) {
-                const uint4 P = lds128(s_par + i * 16u);
-                if ((P.w & 3u) != 1u) continue;
+            for (unsigned rem = slow; rem; rem &= rem - 1u) {
+                const uint32_t i = (uint32_t)__ffs((int)rem) - 1u;                 // record slot = its role-0 lane
                 const uint32_t kk = i >= tp ? 1u : 0u, pp = tile * tp + (i - kk * tp);
-                emit_generic(b, (int)kk, pp, b.cls[pp], P.x, lane);
+                emit_generic(b, (int)kk, pp, b.cls[pp], lds32(s_par + i * 32u), lane);
             }
         }
         __syncwarp();
