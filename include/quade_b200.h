@@ -79,6 +79,10 @@ typedef struct {
     uint64_t ticket; /* caller's tag, returned by collect */
 } quade_batch;
 
+/* kernel stages timed per batch (ms_kernel[]).  FRAME: k_frame6 (newline scan, record framing, index digest);
+ * VALIDATE: what turns its per-tile output into per-record arrays -- k_tilescan, k_densify, the redo pass for tiles
+ * whose text defeated the record-start guess, and k_fix_* for files with len(seq) != len(qual) records
+ * (FastqReader.py:48-50); PAIRING .. COMPACT: one kernel each (BINSCAN: two). */
 enum { QUADE_K_FRAME = 0, QUADE_K_VALIDATE, QUADE_K_PAIRING, QUADE_K_CLASSIFY, QUADE_K_BINSCAN, QUADE_K_OFFSETS,
        QUADE_K_COMPACT, QUADE_K_COUNT };
 
