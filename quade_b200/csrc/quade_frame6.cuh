@@ -23,6 +23,9 @@ namespace quade {
 namespace {
 
 constexpr int F6T = 256;
+#ifndef F6_MINB
+#define F6_MINB 6
+#endif
 constexpr uint32_t F6_BLANK = 1u << 25;        // scratch digest: the header had no name token
 
 // ---- record parser without the candidate bitmap ------------------------------------------------------------
@@ -95,7 +98,7 @@ __device__ __forceinline__ F2Rec f6_parse(const F2Tile &t, uint32_t hs, const ui
 }
 
 template <bool REDO>
-__global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ BatchDev b, uint32_t total_tiles)
+__global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__ BatchDev b, uint32_t total_tiles)
 {
     extern __shared__ __align__(128) uint8_t f6_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -184,18 +187,27 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
             const bool edge = T.win < (uint32_t)F2_WIN;         // the window reaches the end of the buffer
             uint32_t vbit = F2_NONE;                            // window offset of a virtual last line end
             if (edge && T.last && T.n > 0u && T.n - T.tbase < (uint32_t)F2_WIN) vbit = T.n - T.tbase;
+            if (!edge) {                                        // the usual tile: nothing to clip
 #pragma unroll
-            for (uint32_t i = 0; i < 5; ++i) {
-                const uint32_t c = (uint32_t)tid + (uint32_t)F6T * i, off = 16u * c;
-                if (i == 4 && tid >= F2_HALO / 16) break;       // halo: 128 chunks, warps 0-3
-                const uint4 q = lds128(sm0 + off);
-                uint32_t m = f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w));
-                if (edge) {
+                for (uint32_t i = 0; i < 5; ++i) {
+                    const uint32_t c = (uint32_t)tid + (uint32_t)F6T * i;
+                    if (i == 4 && tid >= F2_HALO / 16) break;   // halo: 128 chunks, warps 0-3
+                    const uint4 q = lds128(sm0 + 16u * c);
+                    sts16(sm0 + F3_OFF_BM + 2u * c,
+                          f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w)));
+                }
+            } else {
+#pragma unroll 1
+                for (uint32_t i = 0; i < 5; ++i) {
+                    const uint32_t c = (uint32_t)tid + (uint32_t)F6T * i, off = 16u * c;
+                    if (i == 4 && tid >= F2_HALO / 16) break;
+                    const uint4 q = lds128(sm0 + off);
+                    uint32_t m = f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w));
                     const uint32_t keep = off >= T.win ? 0u : (T.win - off >= 16u ? 0xffffu : (1u << (T.win - off)) - 1u);
                     m &= keep;
                     if ((vbit >> 4) == c && f2_byte(T, T.n - 1u) != '\n') m |= 1u << (vbit & 15u);   // no final '\n'
+                    sts16(sm0 + F3_OFF_BM + 2u * c, m);
                 }
-                sts16(sm0 + F3_OFF_BM + 2u * c, m);
             }
         }
         __syncthreads();                                        // B1: bitmaps complete
@@ -280,21 +292,25 @@ __global__ void __launch_bounds__(F6T, 6) k_frame6(const __grid_constant__ Batch
         }
         __syncthreads();                                        // B3: list complete
 
-        // 4. which list entries close a record: the true k0 (redo) or the guess from the text
-        uint32_t t0 = 3u, k0 = 0u;                              // list index of the first record-closing line
-        if (REDO) {
-            k0 = st.tile_tab[lt].x;
-            t0 = (3u - k0) & 3u;
-        } else if (lt != 0u) {
-            bool ok = false;
-            if (lane < 4 && (uint32_t)lane + 2u < npos)
-                ok = lds8(sm0 + lds16(a_pos + 2u * lane) + 1u) == '@' && lds8(sm0 + lds16(a_pos + 2u * (lane + 2)) + 1u) == '+';
-            const unsigned g = __ballot_sync(0xffffffffu, ok);
-            t0 = g ? (uint32_t)__ffs((int)g) - 1u : 0u;
+        // 4. which list entries close a record: the true k0 (redo) or the guess from the text.  Only the warps that
+        //    can own a record of this tile take part (insert reads: 47 records per tile = 2 of 8 warps).
+        const bool warp_has = (uint32_t)warp * 32u < first + ((total + 3u) >> 2);
+        uint32_t t0 = 3u, k0 = 0u, nslot = 0u, rbase = 0u;      // t0: list index of the first record-closing line
+        if (warp_has || warp == 0) {
+            if (REDO) {
+                k0 = st.tile_tab[lt].x;
+                t0 = (3u - k0) & 3u;
+            } else if (lt != 0u) {
+                bool ok = false;
+                if (lane < 4 && (uint32_t)lane + 2u < npos)
+                    ok = lds8(sm0 + lds16(a_pos + 2u * lane) + 1u) == '@' && lds8(sm0 + lds16(a_pos + 2u * (lane + 2)) + 1u) == '+';
+                const unsigned g = __ballot_sync(0xffffffffu, ok);
+                t0 = g ? (uint32_t)__ffs((int)g) - 1u : 0u;
+            }
+            nslot = first + (total > t0 ? (total - t0 + 3u) >> 2 : 0u);
+            rbase = lt == 0u ? 0u : (k0 >> 2) + 1u;             // REDO: record index of slot 0
+            if (!REDO && tid == 0) st.tile_tab[lt] = make_uint4(total, t0, nslot, s_misc[9]);
         }
-        const uint32_t nslot = first + (total > t0 ? (total - t0 + 3u) >> 2 : 0u);
-        const uint32_t rbase = lt == 0u ? 0u : (k0 >> 2) + 1u;  // REDO: record index of slot 0
-        if (!REDO && tid == 0) st.tile_tab[lt] = make_uint4(total, t0, nslot, s_misc[9]);
 
         // record of slot i (FastqReader.py:37-44); false: only the redo pass can find it (line-end list overflow)
         auto parse_slot = [&](uint32_t slot, F2Rec &R) -> bool {
