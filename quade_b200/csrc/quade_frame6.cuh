@@ -96,6 +96,51 @@ __device__ __forceinline__ F2Rec f6_parse(const F2Tile &t, uint32_t hs, const ui
     r.valid = r.seq_len == f6_rstrip(t, r.qual_off, nl3) - r.qual_off;
     return r;
 }
+// f2_digest with the bytes taken straight from the staged window when the whole record lies inside it (always,
+// except for records longer than the 2 KiB halo): no per-byte window check
+template <bool INWIN>
+__device__ __forceinline__ void f6_digest_t(const BatchDev &b, const StreamDev &st, int s, const F2Tile &t, const F2Rec &r, uint32_t v)
+{
+    auto byte_at = [&](uint32_t pos) -> uint32_t { return INWIN ? lds8(t.sdata + (pos - t.tbase)) : f2_byte(t, pos); };
+    uint32_t ia, in, ma, mn;
+    f2_clamp(b.span[s - 2], r.seq_len, &ia, &in);          // QUADE_SPAN_IDX1 / IDX2
+    f2_clamp(b.span[s], r.seq_len, &ma, &mn);              // QUADE_SPAN_MOL1 / MOL2
+    u64 key = 0;
+    uint32_t nm = 0, bad = in > 32u ? 1u : 0u, minq = 255u;
+    uint8_t *slot = st.sfx + (size_t)v * st.sfx_slot;
+    uint32_t word = 0;
+    for (uint32_t i = 0; i < in; ++i) {
+        uint32_t c = byte_at(r.seq_off + ia + i);
+        const uint32_t q = byte_at(r.qual_off + ia + i);
+        minq = q < minq ? q : minq;                         // phred = q - 33 (FastqSeq.py:44), compared later
+        word |= c << ((i & 3u) * 8u);
+        if ((i & 3u) == 3u || i + 1u == in) {
+            *reinterpret_cast<uint32_t *>(slot + (i & ~3u)) = word;
+            word = 0;
+        }
+        if (c - 'a' < 26u) c -= 32u;                        // index.seq.upper() (Sample.py:65)
+        const bool acgt = c == 'A' || c == 'C' || c == 'G' || c == 'T';
+        if (!acgt && c != 'N') bad = 1u;
+        if (i < 32u) {
+            if (acgt) key |= (u64)((c >> 1) & 3u) << (2u * i);
+            else if (c == 'N') nm |= 1u << i;
+        }
+    }
+    uint8_t *mslot = slot + ((st.wi + 3u) & ~3u);
+    for (uint32_t i = 0; i < mn; ++i) {
+        word |= byte_at(r.seq_off + ma + i) << ((i & 3u) * 8u);
+        if ((i & 3u) == 3u || i + 1u == mn) {
+            *reinterpret_cast<uint32_t *>(mslot + (i & ~3u)) = word;
+            word = 0;
+        }
+    }
+    st.dig[v] = make_uint4((uint32_t)key, (uint32_t)(key >> 32), nm, in | mn << 8 | minq << 16 | bad << 24);
+}
+__device__ __forceinline__ void f6_digest(const BatchDev &b, const StreamDev &st, int s, const F2Tile &t, const F2Rec &r, uint32_t v)
+{
+    if (r.seq_off >= t.tbase && r.qual_off + r.seq_len - t.tbase <= t.win) f6_digest_t<true>(b, st, s, t, r, v);
+    else f6_digest_t<false>(b, st, s, t, r, v);
+}
 
 template <bool REDO>
 __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__ BatchDev b, uint32_t total_tiles)
@@ -347,7 +392,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
                 } else if (inv) {
                     st.dig[v] = make_uint4(0u, 0u, 0u, inv);
                 } else {
-                    f2_digest(b, st, s, T, R, v);
+                    f6_digest(b, st, s, T, R, v);
                 }
             } else {
                 st.vend_t[v] = R.end;
@@ -360,7 +405,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
                     StreamDev stt = st;
                     stt.dig = st.dig_t;
                     stt.sfx = st.sfx_t;
-                    f2_digest(b, stt, s, T, R, v);
+                    f6_digest(b, stt, s, T, R, v);
                     if (R.nlen == 0u) st.dig_t[v].w |= F6_BLANK;
                 }
             }
