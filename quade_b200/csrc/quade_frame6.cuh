@@ -118,12 +118,16 @@ __device__ __forceinline__ void f6_digest_t(const BatchDev &b, const StreamDev &
             *reinterpret_cast<uint32_t *>(slot + (i & ~3u)) = word;
             word = 0;
         }
-        if (c - 'a' < 26u) c -= 32u;                        // index.seq.upper() (Sample.py:65)
-        const bool acgt = c == 'A' || c == 'C' || c == 'G' || c == 'T';
-        if (!acgt && c != 'N') bad = 1u;
+        // index.seq.upper() (Sample.py:65) and the base class in 4 instructions: (c >> 1) & 3 maps A,C,T,G (either
+        // case) to 0,1,2,3; c is one of them iff c with bit 5 cleared equals the letter of its code (clearing bit 5
+        // turns only 'a'..'z' into 'A'..'Z' among the bytes that can end up equal to a capital letter)
+        const uint32_t code = (c >> 1) & 3u, up = c & 0xdfu;
+        const bool acgt = up == ((0x47544341u >> (8u * code)) & 0xffu);
+        const bool isn = up == 'N';
+        if (!acgt && !isn) bad = 1u;
         if (i < 32u) {
-            if (acgt) key |= (u64)((c >> 1) & 3u) << (2u * i);
-            else if (c == 'N') nm |= 1u << i;
+            if (acgt) key |= (u64)code << (2u * i);
+            else if (isn) nm |= 1u << i;
         }
     }
     uint8_t *mslot = slot + ((st.wi + 3u) & ~3u);
