@@ -629,6 +629,41 @@ __global__ void __launch_bounds__(C2T) k_classify2(const __grid_constant__ Batch
             const uint32_t suf_len = 1u + klen + (mlen ? 1u + mlen : 0u) + 1u;
             const uint8_t *s1 = i1.sfx + (size_t)p * i1.sfx_slot, *s2 = b.dual ? i2.sfx + (size_t)p * i2.sfx_slot : s1;
             uint32_t *suf = reinterpret_cast<uint32_t *>(b.suffix + (size_t)p * b.suf_cap);
+            if (in1 <= 8u && in2 <= 8u && mn1 <= 8u && mn2 <= 8u) {
+                // every piece fits a 64-bit word (the usual 6..10-base indexes): pieces are appended to a 64-bit
+                // accumulator by shifts and flushed with 8-byte stores -- ~80 instructions instead of ~670 for the
+                // byte-wise assembly below, and 4 independent 8-byte loads instead of ~30 dependent byte loads
+                auto piece = [](const uint8_t *q, uint32_t n) -> u64 {          // n <= 8 bytes at a 4-byte aligned address
+                    const uint32_t *w = reinterpret_cast<const uint32_t *>(q);
+                    const u64 v = n ? ((u64)w[0] | (n > 4u ? (u64)w[1] << 32 : 0ull)) : 0ull;
+                    return n >= 8u ? v : v & ((1ull << (8u * n)) - 1ull);
+                };
+                const u64 pa = piece(s1, in1), pb = b.dual ? piece(s2, in2) : 0ull;
+                const u64 pc = piece(s1 + mo1, mn1), pd = b.dual ? piece(s2 + mo2, mn2) : 0ull;
+                u64 *suf64 = reinterpret_cast<u64 *>(suf);
+                u64 acc = ':';
+                uint32_t fill = 1, wq = 0;                                       // bytes in acc, 8-byte words flushed
+                auto append = [&](u64 v, uint32_t n) {
+                    if (!n) return;
+                    acc |= v << (8u * fill);                                     // fill < 8 here
+                    if (fill + n >= 8u) {
+                        suf64[wq++] = acc;
+                        acc = fill ? v >> (8u * (8u - fill)) : 0ull;
+                        fill = fill + n - 8u;
+                    } else {
+                        fill += n;
+                    }
+                };
+                append(pa, in1);
+                append(pb, in2);
+                if (mlen) {
+                    append((u64)':', 1u);
+                    append(pc, mn1);
+                    append(pd, mn2);
+                }
+                append((u64)'\n', 1u);
+                if (fill) suf64[wq] = acc;
+            } else
             for (uint32_t w0 = 0; w0 < suf_len; w0 += 4) {
                 uint32_t word = 0;
 #pragma unroll
