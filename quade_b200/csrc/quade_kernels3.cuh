@@ -20,23 +20,28 @@ __global__ void __launch_bounds__(1024) k_binscan_blocks(const __grid_constant__
     uint32_t *h = b.hist + col;
     u64 sum = 0;
     if (on) {
-        uint32_t k = k0;
-        for (; k + 4 <= k1; k += 4) {
-            const uint32_t v0 = h[(size_t)(k + 0) * width], v1 = h[(size_t)(k + 1) * width];
-            const uint32_t v2 = h[(size_t)(k + 2) * width], v3 = h[(size_t)(k + 3) * width];
-            sum += (u64)v0 + v1 + v2 + v3;
+        for (uint32_t kb = k0; kb < k1; kb += 8u) {
+            uint32_t v[8];
+#pragma unroll
+            for (uint32_t q = 0; q < 8; ++q) v[q] = kb + q < k1 ? h[(size_t)(kb + q) * width] : 0u;
+#pragma unroll
+            for (uint32_t q = 0; q < 8; ++q) sum += v[q];
         }
-        for (; k < k1; ++k) sum += h[(size_t)k * width];
     }
     s_part[sl][threadIdx.x] = sum;
     __syncthreads();
     u64 run = 0;
     for (uint32_t i = 0; i < sl; ++i) run += s_part[i][threadIdx.x];
     if (on) {
-        for (uint32_t k = k0; k < k1; ++k) {
-            const uint32_t v = h[(size_t)k * width];
-            h[(size_t)k * width] = (uint32_t)run;
-            run += v;
+        for (uint32_t kb = k0; kb < k1; kb += 8u) {           // 8 rows loaded at once (independent), then rewritten
+            uint32_t v[8];
+#pragma unroll
+            for (uint32_t q = 0; q < 8; ++q) v[q] = kb + q < k1 ? h[(size_t)(kb + q) * width] : 0u;
+#pragma unroll
+            for (uint32_t q = 0; q < 8; ++q) {
+                if (kb + q < k1) h[(size_t)(kb + q) * width] = (uint32_t)run;
+                run += v[q];
+            }
         }
         if (sl == 31) b.bin_total[col] = run;   // the last slice ends on the column total
     }
