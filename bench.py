@@ -44,7 +44,8 @@ def parse_args():
     ap.add_argument("--cpu-pairs", type=int, default=1_000_000, help="sample size of the CPU baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--slots", type=int, default=3, help="batch slots in flight (submit/collect ring)")
+    ap.add_argument("--slots", type=int, default=6,
+                    help="batch slots in flight (submit/collect ring): the device queue rides out host hiccups of (slots-1) steps")
     ap.add_argument("--spinup-ms", type=float, default=400.0,
                     help="untimed extra warm-up before the W warm-up steps: the GPU sits idle while the inputs are generated "
                          "on the host and needs tens of ms of load to be back at full clocks")
@@ -200,13 +201,19 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    diag = []                                              # (seconds, what) of every host call, QUADE_BENCH_DIAG=1
+
     def device_steps(n):
-        """n batches back to back, two in flight; returns the collected results."""
+        """n batches back to back, args.slots in flight; returns the collected results."""
         res = []
         for i in range(n):
             if ctx.in_flight == args.slots:
+                t = time.perf_counter()
                 res.append(ctx.collect())
+                diag.append((time.perf_counter() - t, "collect"))
+            t = time.perf_counter()
             ctx.submit_device(ptrs, sizes, last=True, ticket=i)
+            diag.append((time.perf_counter() - t, "submit"))
         while ctx.in_flight:
             res.append(ctx.collect())
         return res
@@ -220,7 +227,11 @@ def run_ours(args, rank, world, local_rank):
     sampler.begin()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
+    del diag[:]
     results = device_steps(args.steps)
+    if os.environ.get("QUADE_BENCH_DIAG"):
+        print("diag: slowest host calls in the timed region (ms):",
+              [(round(a * 1e3, 2), w) for a, w in sorted(diag, reverse=True)[:4]], file=sys.stderr)
     counters = torch.from_numpy(ctx.counters()).to(dev)
     if world > 1:
         dist.all_reduce(counters)          # the path's only collective: the report counters (NCCL)
@@ -262,7 +273,7 @@ def run_ours(args, rank, world, local_rank):
         def host_steps(n):
             done = 0
             for i in range(n):
-                if ctx.in_flight == args.slots:
+                if ctx.in_flight == min(args.slots, 3):                # PCIe-bound: a deeper ring only adds pinned memory
                     r = ctx.collect()
                     done += int(r.arena(0)[-1]) * 0 + r.n_pairs      # touches the copied-back result
                 ctx.submit(host, last=True, ticket=i)
@@ -270,7 +281,7 @@ def run_ours(args, rank, world, local_rank):
                 r = ctx.collect()
                 done += int(r.arena(1)[-1]) * 0 + r.n_pairs
             return done
-        host_steps(max(args.slots + 1, args.warmup))       # every slot's pinned output arena exists before timing
+        host_steps(max(args.slots + 1, args.warmup))           # every slot's pinned output arena exists before timing
         barrier()
         t0 = time.perf_counter()
         done = host_steps(args.steps)

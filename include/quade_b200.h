@@ -61,7 +61,7 @@ typedef struct {
     /* capacities of one batch (0 = defaults: 256 MiB per stream, max_stream_bytes/64 pairs) */
     uint64_t max_stream_bytes;
     uint64_t max_pairs;
-    int32_t n_slots;            /* batches in flight (1..4, 0 = 2): submit N+1 while batch N is collected */
+    int32_t n_slots;            /* batches in flight (1..8, 0 = 2): submit N+1 while batch N is collected */
     int32_t reserved;
 } quade_params;
 

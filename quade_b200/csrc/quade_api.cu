@@ -281,7 +281,7 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->n_streams = p->dual ? 4 : 3;
     c->n_bins = 1 + 2 * p->n_samples;
     c->n_slots = p->n_slots ? p->n_slots : 2;
-    if (c->n_slots < 1 || c->n_slots > 4) { delete c; return fail(QUADE_ERR_ARG, "n_slots must be 1..4"); }
+    if (c->n_slots < 1 || c->n_slots > 8) { delete c; return fail(QUADE_ERR_ARG, "n_slots must be 1..8"); }
     c->cap_bytes = p->max_stream_bytes ? p->max_stream_bytes : (256ull << 20);
     c->cap_bytes = (c->cap_bytes + 255) & ~255ull;
     c->cap_pairs = p->max_pairs ? p->max_pairs : c->cap_bytes / 64;
