@@ -73,6 +73,19 @@ __device__ __forceinline__ void emit_generic(const BatchDev &b, int k, uint32_t 
     }
 }
 
+// 16 bytes starting at byte r (0..15) of the 32 bytes {A,B}; r is warp-uniform.  Two levels of uniform selects
+// (r & 4, r & 8) pick the five source words, four funnel shifts align them: 16 instructions, no branch
+__device__ __forceinline__ uint4 shift_bytes_sel(const uint4 A, const uint4 B, uint32_t r)
+{
+    const bool b0 = (r & 4u) != 0u, b1 = (r & 8u) != 0u;
+    const uint32_t u0 = b0 ? A.y : A.x, u1 = b0 ? A.z : A.y, u2 = b0 ? A.w : A.z, u3 = b0 ? B.x : A.w, u4 = b0 ? B.y : B.x,
+                   u5 = b0 ? B.z : B.y, u6 = b0 ? B.w : B.z;
+    const uint32_t w0 = b1 ? u2 : u0, w1 = b1 ? u3 : u1, w2 = b1 ? u4 : u2, w3 = b1 ? u5 : u3, w4 = b1 ? u6 : u4;
+    const uint32_t sh = (r & 3u) * 8u;
+    return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
+                      __funnelshift_r(w3, w4, sh));
+}
+
 struct TileMeta {
     uint4 rc;          // this lane's record {name_off, seq_off, qual_off, seq_len}
     uint32_t nlen, cls, ooff;
@@ -258,7 +271,7 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
             {
                 const uint32_t v = lane, y0 = 16u * v;
                 const uint32_t sa = ((y0 < hend ? hbi : sb) + y0) & ~15u;
-                const uint4 val = shift_bytes(lds128(sa), lds128(sa + 16u), sr);
+                const uint4 val = shift_bytes_sel(lds128(sa), lds128(sa + 16u), sr);
                 if (v >= vlo && v < F1) *reinterpret_cast<uint4 *>(gdst + y0) = val;
             }
             if (F1 > 32u) {                                                        // records longer than 512 bytes
