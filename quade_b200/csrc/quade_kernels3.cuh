@@ -118,15 +118,20 @@ __global__ void __launch_bounds__(256) k_offsets(const __grid_constant__ BatchDe
         const bool active = p < end;
         const uint32_t bin = active ? (b.cls[p] & 0xffffu) : 0xffffffffu;
         const uint32_t l1 = active ? b.len1[p] : 0u, l2 = active ? b.len2[p] : 0u;
+        // stable rank inside the warp: output bytes of the lower lanes that go to the same bin.  match.any gives
+        // the lanes sharing this lane's bin; groups are small (hundreds of bins), so the loop runs 1-3 times
+        // instead of the 32 x 3 shuffles of an all-pairs comparison
+        const unsigned peers = __match_any_sync(0xffffffffu, bin);
+        const bool later = (peers >> lane) > 1u;                // a higher lane writes to the same bin
+        unsigned rem = peers & ((1u << lane) - 1u);
         uint32_t pre1 = 0, pre2 = 0;
-        bool later = false;
-#pragma unroll 8
-        for (int i = 0; i < 32; ++i) {
-            const uint32_t bi = __shfl_sync(0xffffffffu, bin, i);
-            const uint32_t a1 = __shfl_sync(0xffffffffu, l1, i), a2 = __shfl_sync(0xffffffffu, l2, i);
-            if (bi == bin) {
-                if (i < lane) { pre1 += a1; pre2 += a2; }
-                else if (i > lane) later = true;
+        while (__any_sync(0xffffffffu, rem != 0u)) {
+            const int j = rem ? __ffs((int)rem) - 1 : 0;
+            const uint32_t a1 = __shfl_sync(0xffffffffu, l1, j), a2 = __shfl_sync(0xffffffffu, l2, j);
+            if (rem) {
+                pre1 += a1;
+                pre2 += a2;
+                rem &= rem - 1u;
             }
         }
         for (int w = 0; w < 8; ++w) {
