@@ -60,7 +60,8 @@ struct quade_ctx {
     uint64_t cap_bytes = 0, cap_pairs = 0, cap_rec = 0;
     uint32_t suf_cap = 4, pairs_per_block = 4096, cap_blocks = 1;
     uint64_t out_cap = 0;
-    cudaStream_t s_copy = nullptr, s_compute = nullptr, s_d2h = nullptr;
+    cudaStream_t s_copy = nullptr, s_compute = nullptr, s_d2h = nullptr, s_back = nullptr;
+    bool overlap = false;                // k_compact3 of batch i on s_back beside the framing of batch i + 1
     std::vector<Slot> slots;
     int head = 0, tail = 0, in_flight = 0;
     bool samples_set = false;
@@ -300,10 +301,12 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->cumulative.assign(c->n_bins, 0);
     if (const char *v = getenv("QUADE_COMPACT")) set_compact_variant(atoi(v));
     if (const char *v = getenv("QUADE_FRAME")) set_frame_variant(atoi(v));
+    if (const char *v = getenv("QUADE_OVERLAP")) c->overlap = atoi(v) != 0 && c->n_slots >= 2;
     int rc = QUADE_OK;
     if (cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking) != cudaSuccess)
+        cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->s_back, cudaStreamNonBlocking) != cudaSuccess)
         rc = fail(QUADE_ERR_CUDA, "cudaStreamCreate failed");
     c->slots.resize(c->n_slots);
     for (int i = 0; i < c->n_slots && rc == QUADE_OK; ++i) rc = slot_alloc(c, c->slots[i]);
@@ -329,6 +332,7 @@ extern "C" int quade_ctx_destroy(quade_ctx *c)
     if (c->s_copy) cudaStreamDestroy(c->s_copy);
     if (c->s_compute) cudaStreamDestroy(c->s_compute);
     if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
+    if (c->s_back) cudaStreamDestroy(c->s_back);
     delete c;
     return QUADE_OK;
 }

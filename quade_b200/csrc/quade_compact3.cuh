@@ -20,8 +20,9 @@
 namespace quade {
 namespace {
 
-constexpr int C3_TP = 8;                  // pairs per tile (upper bound; the batch's value is in BatchState)
-constexpr int C3_CAP = 3072;              // staged bytes per stream per stage
+constexpr int C3_TP = kCompactTilePairs;                  // pairs per tile (upper bound; the batch's value is in BatchState)
+static_assert(C3_TP >= 1 && C3_TP <= 8, "k_compact3: one record lane per read of the tile, 16 record lanes");
+constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stream per stage
 constexpr int C3_HS = 176;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
 constexpr int C3_SUFV = 4;                // staged suffix: up to 64 bytes per pair
 constexpr int C3_STAGES = 1;               // 1: more resident warps hide the copy latency; 2: per-warp prefetch

@@ -22,6 +22,14 @@ namespace quade {
 
 constexpr int kMaxStreams = 4;
 constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
+#ifndef QUADE_C3_TP
+#define QUADE_C3_TP 8            /* 2 * TP records <= 16 record lanes of k_compact3 */
+#endif
+#ifndef QUADE_C3_CAP
+#define QUADE_C3_CAP 3072
+#endif
+constexpr int kCompactTilePairs = QUADE_C3_TP;   // k_compact3: pairs per tile (upper bound) ...
+constexpr int kCompactStageBytes = QUADE_C3_CAP; // ... and staged bytes per read stream and tile
 constexpr int kTileChunk = 1024;   // k_frame6 / k_tilescan: tiles per chunk of the tile table (16 MiB of input)
 constexpr int kMaxChunks = 256;    // >= kMaxStreamBytes / (16 KiB * kTileChunk)
 

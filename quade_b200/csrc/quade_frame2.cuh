@@ -552,12 +552,12 @@ __global__ void k_pairing2(const __grid_constant__ BatchDev b)
             if (parsed) S->err_blank = 1u;
         }
     }
-    uint32_t tp = 8;                                            // k_compact3 tile size from the mean record size
+    uint32_t tp = kCompactTilePairs;                                            // k_compact3 tile size from the mean record size
     if (np > 0) {
         uint32_t avg = max(S->consumed[0], S->consumed[1]) / np + 1u;
         avg += avg / 8u;
-        tp = (3072u - 48u) / avg;
-        tp = tp > 8u ? 8u : (tp < 1u ? 1u : tp);
+        tp = ((uint32_t)kCompactStageBytes - 48u) / avg;
+        tp = tp > (uint32_t)kCompactTilePairs ? (uint32_t)kCompactTilePairs : (tp < 1u ? 1u : tp);
     }
     S->compact_tp = tp;
     S->n_pairs = np;

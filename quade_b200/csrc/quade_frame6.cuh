@@ -493,47 +493,84 @@ __global__ void __launch_bounds__(kTileChunk) k_tilescan(const __grid_constant__
 // k_densify: one warp per tile, scratch -> dense per-record arrays at the true record index (the pairing ordinal
 // of a file without invalid records).  Counts the records with len(seq) != len(qual), finds the first blank header.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_densify(const __grid_constant__ BatchDev b, uint32_t total_tiles)
+__global__ void __launch_bounds__(256, 4) k_densify(const __grid_constant__ BatchDev b, uint32_t total_tiles)
 {
     const int lane = threadIdx.x & 31;
     BatchState *S = b.state;
     const uint32_t nwarps = gridDim.x * (blockDim.x >> 5);
-    for (uint32_t tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); tile < total_tiles; tile += nwarps) {
-        int s = 0;
+    auto locate = [&](uint32_t tile, int &s, uint32_t &lt) -> uint4 {
+        s = 0;
 #pragma unroll
         for (int i = 1; i < kMaxStreams; ++i) s += (i < b.n_streams && tile >= b.frame_tile_start[i]) ? 1 : 0;
-        const uint32_t lt = tile - b.frame_tile_start[s];
+        lt = tile - b.frame_tile_start[s];
+        return b.st[s].tile_tab[lt];
+    };
+    uint32_t tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (tile >= total_tiles) return;
+    int s, s_next = 0;
+    uint32_t lt, lt_next = 0u;
+    uint4 e = locate(tile, s, lt), e_next = make_uint4(0u, 0u, 0u, 0u);
+    for (;; tile += nwarps, e = e_next, s = s_next, lt = lt_next) {
+        if (tile >= total_tiles) break;
+        if (tile + nwarps < total_tiles) e_next = locate(tile + nwarps, s_next, lt_next);   // a tile ahead
         const StreamDev &st = b.st[s];
-        const uint4 e = st.tile_tab[lt];
         if (!(e.y & 1u) || e.z == 0u) continue;
         const uint32_t rbase = lt == 0u ? 0u : (e.x >> 2) + 1u, n_rec = S->n_lines[s] >> 2, sv = st.sfx_slot >> 4;
-        for (uint32_t i = lane; i < e.z; i += 32) {
-            const uint32_t j = rbase + i, v = e.w + i;
-            if (j >= n_rec) continue;                           // trailing partial record (FastqReader.py:57-58)
-            if (j >= st.cap_rec) { S->err_capacity = 1u; continue; }
-            st.vend[j] = st.vend_t[v];
-            bool blank, inv;
-            if (s < 2) {
-                const uint4 r = st.rec_t[v];
-                const uint32_t nl = st.vnlen_t[v];
-                st.rec[j] = r;
-                st.vnlen[j] = nl;
-                blank = nl == 0u;
-                inv = (r.w >> 31) != 0u;
-            } else {
-                uint4 d = st.dig_t[v];
-                blank = (d.w & F6_BLANK) != 0u;
-                inv = (d.w >> 31) != 0u;
-                d.w &= ~F6_BLANK;
-                st.dig[j] = d;
-                if (!inv) {
-                    const uint4 *src = reinterpret_cast<const uint4 *>(st.sfx_t + (size_t)v * st.sfx_slot);
-                    uint4 *dst = reinterpret_cast<uint4 *>(st.sfx + (size_t)j * st.sfx_slot);
-                    for (uint32_t q = 0; q < sv; ++q) dst[q] = src[q];
+        // Two records per lane and pass; every load of a pass is issued before its first store (the arrays may
+        // alias as far as the compiler knows, and a load -> store -> load chain costs one DRAM round trip per link).
+        for (uint32_t i0 = lane; i0 < e.z; i0 += 64) {
+            uint32_t j[2], v[2];
+            bool act[2];
+            uint32_t ve[2];
+            uint4 r[2], x0[2], x1[2];
+            uint32_t nl[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const uint32_t i = i0 + 32u * u;
+                j[u] = rbase + i;
+                v[u] = e.w + i;
+                act[u] = i < e.z && j[u] < n_rec;               // trailing partial record (FastqReader.py:57-58)
+                if (act[u] && j[u] >= st.cap_rec) { S->err_capacity = 1u; act[u] = false; }
+                nl[u] = 0u;
+                x0[u] = x1[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (act[u]) {
+                    ve[u] = st.vend_t[v[u]];
+                    if (s < 2) {
+                        r[u] = st.rec_t[v[u]];
+                        nl[u] = st.vnlen_t[v[u]];
+                    } else {
+                        r[u] = st.dig_t[v[u]];
+                        const uint4 *src = reinterpret_cast<const uint4 *>(st.sfx_t + (size_t)v[u] * st.sfx_slot);
+                        if (sv > 0u) x0[u] = src[0];
+                        if (sv > 1u) x1[u] = src[1];
+                    }
                 }
             }
-            if (blank) atomicMax(&S->first_blank[s], ~j);       // keeps the LOWEST blank record index
-            if (inv) atomicAdd(&S->n_invalid[s], 1u);
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (!act[u]) continue;
+                st.vend[j[u]] = ve[u];
+                bool blank;
+                const bool inv = (r[u].w >> 31) != 0u;
+                if (s < 2) {
+                    st.rec[j[u]] = r[u];
+                    st.vnlen[j[u]] = nl[u];
+                    blank = nl[u] == 0u;
+                } else {
+                    blank = (r[u].w & F6_BLANK) != 0u;
+                    r[u].w &= ~F6_BLANK;
+                    st.dig[j[u]] = r[u];
+                    if (!inv) {
+                        const uint4 *src = reinterpret_cast<const uint4 *>(st.sfx_t + (size_t)v[u] * st.sfx_slot);
+                        uint4 *dst = reinterpret_cast<uint4 *>(st.sfx + (size_t)j[u] * st.sfx_slot);
+                        if (sv > 0u) dst[0] = x0[u];
+                        if (sv > 1u) dst[1] = x1[u];
+                        for (uint32_t q = 2; q < sv; ++q) dst[q] = src[q];
+                    }
+                }
+                if (blank) atomicMax(&S->first_blank[s], ~j[u]);    // keeps the LOWEST blank record index
+                if (inv) atomicAdd(&S->n_invalid[s], 1u);
+            }
         }
     }
 }

@@ -107,12 +107,12 @@ __global__ void k_pairing(const __grid_constant__ BatchDev b)
     }
     if (S->err_capacity) np = 0;
     // k_compact3 stages the R1 / R2 spans of a tile of tp pairs: size tp from the mean record size
-    uint32_t tp = 8;
+    uint32_t tp = kCompactTilePairs;
     if (np > 0) {
         uint32_t avg = max(S->consumed[0], S->consumed[1]) / np + 1u;
         avg += avg / 8u;
-        tp = (3072u - 48u) / avg;
-        tp = tp > 8u ? 8u : (tp < 1u ? 1u : tp);
+        tp = ((uint32_t)kCompactStageBytes - 48u) / avg;
+        tp = tp > (uint32_t)kCompactTilePairs ? (uint32_t)kCompactTilePairs : (tp < 1u ? 1u : tp);
     }
     S->compact_tp = tp;
     S->n_pairs = np;

@@ -12,9 +12,13 @@ void set_frame_variant(int v) { g_frame_variant = v; }
 int frame_variant() { return g_frame_variant; }
 int frame_launches() { return g_frame_variant == 10 ? 4 : 1; }   // k_frame6, k_tilescan, k_densify, k_frame6<redo>
 
+static int g_f6_ctas = 0, g_c3_ctas = 0;    // CTAs per SM when k_frame6 and k_compact3 share the SMs (0: all that fit)
+
 static void init_launch_config()
 {
     if (g_sms) return;
+    if (const char *v = getenv("QUADE_F6_CTAS")) g_f6_ctas = atoi(v);
+    if (const char *v = getenv("QUADE_C3_CTAS")) g_c3_ctas = atoi(v);
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
@@ -79,7 +83,7 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ6, k_frame6<false>, F6T, F3_SMEM);
             if (occ6 < 1) occ6 = 1;
         }
-        uint32_t g6 = (uint32_t)(g_sms * occ6);
+        uint32_t g6 = (uint32_t)(g_sms * (g_f6_ctas > 0 && g_f6_ctas < occ6 ? g_f6_ctas : occ6));
         if (g6 > total) g6 = total;
         k_frame6<false><<<g6, F6T, F3_SMEM, s>>>(b, total);
         return;
@@ -234,7 +238,7 @@ void launch_compact(const BatchDev &b, cudaStream_t s)
 {
     init_launch_config();
     if (g_compact_variant == 3) {
-        uint32_t grid3 = (uint32_t)(g_sms * g_occ_compact3);
+        uint32_t grid3 = (uint32_t)(g_sms * (g_c3_ctas > 0 && g_c3_ctas < g_occ_compact3 ? g_c3_ctas : g_occ_compact3));
         if (grid3 > b.cap_pairs) grid3 = b.cap_pairs;
         if (grid3 < 1) grid3 = 1;
         k_compact3<<<grid3, 32, C3_SMEM, s>>>(b);
