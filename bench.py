@@ -166,7 +166,7 @@ def run_reference(args, rank, world):
                              "sample": leg.describe() + " per step"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -329,12 +329,27 @@ def run_ours(args, rank, world, local_rank):
                            "undetermined_frac": und / max(1, tot)},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
 
 
+_JSON_OUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else a library prints (NCCL's version banner under
+    NCCL_DEBUG=VERSION, torchrun notices) has been pointed at stderr by main()."""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
     args = parse_args()
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")      # keep the real stdout for the JSON line ...
+    os.dup2(2, 1)                              # ... and send fd 1 (C libraries included) to stderr
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
