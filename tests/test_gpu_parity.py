@@ -230,3 +230,42 @@ def test_multi_tile_malformed_text_matches_oracle(variant):
     if os.environ.get("QUADE_FRAME", "10") == "10" and variant in ("headers_without_at", "plus_line_text", "tiny_lines"):
         assert r.reframed_tiles > 0, "the wrong-guess path was not exercised"
     ctx.close()
+
+
+def test_full_size_batch_matches_oracle_and_is_split_invariant():
+    """BASELINE.json's step size: ONE batch of 2 M cfg3 pairs (1.7 GB of FASTQ text, the bench workload).
+    (1) byte-identical to the C oracle on the same input; (2) conservation: every pair lands in exactly one bin and
+    the output size is the size of the written records plus their name suffixes; (3) split invariance: the same
+    chunk fed as three ragged batches with carry-over gives the same per-bin streams (compared by digest)."""
+    import hashlib
+    from quade_b200.synth import Synth
+    s = Synth.from_config("cfg3")
+    n = 2_000_000
+    streams = s.generate(0, n)
+    sizes = [len(a) for a in streams]
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    ref = O.demux_batch(p, streams, last=True)
+    ctx, _ = _ctx_for(p, max_stream_bytes=max(sizes) + 4096, max_pairs=n + 1024, n_slots=1)
+    r = ctx.run(streams, last=True)
+    _assert_same(r, ref, p.nbins, "2 M pairs")
+    assert r.n_pairs == n and int(r.counters.sum()) == n and r.reframed_tiles == 0
+    one_shot = [[hashlib.blake2b(r.bin_bytes(k, b), digest_size=16).digest() for b in range(p.nbins)] for k in range(2)]
+    counters = r.counters.copy()
+    # three ragged batches: cut points are arbitrary byte positions, different in every file
+    views = [memoryview(a) for a in streams]
+    cuts = [[0, int(sz * 0.31) + 17 * k, int(sz * 0.64) + 5 * k, sz] for k, sz in enumerate(sizes)]
+    h = [[hashlib.blake2b(digest_size=16) for _ in range(p.nbins)] for _ in range(2)]
+    pos, total, csum = [0] * 4, 0, np.zeros_like(counters)
+    for i in range(1, 4):
+        last = i == 3
+        rb = ctx.run([views[k][pos[k]:cuts[k][i]] for k in range(4)], last=last)
+        total += rb.n_pairs
+        csum += rb.counters
+        for k in range(2):
+            for b in range(p.nbins):
+                h[k][b].update(rb.bin_bytes(k, b))
+        for k in range(4):
+            pos[k] += rb.consumed[k]
+    assert total == n and (csum == counters).all()
+    assert [[x.digest() for x in row] for row in h] == one_shot
+    ctx.close()
