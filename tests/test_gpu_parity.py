@@ -127,6 +127,35 @@ def test_blank_header_is_fatal():
     ctx.close()
 
 
+def test_error_codes_of_the_c_abi():
+    """include/quade_b200.h error enum through the C-ABI: every error leaves the context usable."""
+    from quade_b200 import DemuxContext, QuadeError
+    good = b"@a\nACGT\n+\nIIII\n"
+    spans = [(0, 4), (0, 0), (0, 0), (0, 0)]
+    for keys, code in ((["ACGX"], -3), (["ACGT", "ACGT"], -3), ([""], -3), (["A" * 33], -7)):   # Sample.py:140-141,171-175
+        with pytest.raises(QuadeError) as e:
+            DemuxContext(False, spans, 0, keys, max_stream_bytes=1 << 16, max_pairs=64)
+        assert e.value.code == code, keys
+    ctx = DemuxContext(False, spans, 0, ["ACGT"], max_stream_bytes=1 << 12, max_pairs=32, n_slots=1)
+    with pytest.raises(QuadeError) as e:
+        ctx.collect()                                           # nothing submitted
+    assert e.value.code == -8
+    with pytest.raises(QuadeError) as e:
+        ctx.run([good * 300, good, good])                       # 4500 bytes > max_stream_bytes
+    assert e.value.code == -6
+    with pytest.raises(QuadeError) as e:
+        ctx.run([good * 200, good * 200, good * 200])           # 200 pairs > max_pairs
+    assert e.value.code == -6
+    ctx.submit([good, good, good])
+    with pytest.raises(QuadeError) as e:
+        ctx.submit([good, good, good])                          # the only slot is in flight
+    assert e.value.code == -8
+    assert ctx.collect().n_pairs == 1
+    r = ctx.run([good * 32, good * 32, good * 32])              # exactly max_pairs
+    assert r.n_pairs == 32 and int(r.counters.sum()) == 32
+    ctx.close()
+
+
 def test_empty_and_tiny_batches():
     from quade_b200 import DemuxContext
     ctx = DemuxContext(False, [(0, 4), (0, 0), (0, 0), (0, 0)], 10, ["ACAG"], max_stream_bytes=1 << 16, max_pairs=64)
@@ -232,17 +261,19 @@ def test_multi_tile_malformed_text_matches_oracle(variant):
     ctx.close()
 
 
-def test_full_size_batch_matches_oracle_and_is_split_invariant():
-    """BASELINE.json's step size: ONE batch of 2 M cfg3 pairs (1.7 GB of FASTQ text, the bench workload).
+@pytest.mark.parametrize("name", ["cfg2", "cfg3", "cfg4", "cfg5"])
+def test_full_size_batch_matches_oracle_and_is_split_invariant(name):
+    """BASELINE.json's step size: ONE batch of 2 M pairs (1.5-1.7 GB of FASTQ text; cfg3 is the bench workload).
     (1) byte-identical to the C oracle on the same input; (2) conservation: every pair lands in exactly one bin and
     the output size is the size of the written records plus their name suffixes; (3) split invariance: the same
     chunk fed as three ragged batches with carry-over gives the same per-bin streams (compared by digest)."""
     import hashlib
     from quade_b200.synth import Synth
-    s = Synth.from_config("cfg3")
+    s = Synth.from_config(name)
     n = 2_000_000
     streams = s.generate(0, n)
     sizes = [len(a) for a in streams]
+    ns = len(streams)
     p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
     ref = O.demux_batch(p, streams, last=True)
     ctx, _ = _ctx_for(p, max_stream_bytes=max(sizes) + 4096, max_pairs=n + 1024, n_slots=1)
@@ -255,16 +286,16 @@ def test_full_size_batch_matches_oracle_and_is_split_invariant():
     views = [memoryview(a) for a in streams]
     cuts = [[0, int(sz * 0.31) + 17 * k, int(sz * 0.64) + 5 * k, sz] for k, sz in enumerate(sizes)]
     h = [[hashlib.blake2b(digest_size=16) for _ in range(p.nbins)] for _ in range(2)]
-    pos, total, csum = [0] * 4, 0, np.zeros_like(counters)
+    pos, total, csum = [0] * ns, 0, np.zeros_like(counters)
     for i in range(1, 4):
         last = i == 3
-        rb = ctx.run([views[k][pos[k]:cuts[k][i]] for k in range(4)], last=last)
+        rb = ctx.run([views[k][pos[k]:cuts[k][i]] for k in range(ns)], last=last)
         total += rb.n_pairs
         csum += rb.counters
         for k in range(2):
             for b in range(p.nbins):
                 h[k][b].update(rb.bin_bytes(k, b))
-        for k in range(4):
+        for k in range(ns):
             pos[k] += rb.consumed[k]
     assert total == n and (csum == counters).all()
     assert [[x.digest() for x in row] for row in h] == one_shot
