@@ -47,7 +47,7 @@ def build(force=False, verbose=False):
             print(out)
         if p.returncode != 0:
             raise RuntimeError("nvcc failed: %s\n%s" % (" ".join(cmd), out))
-    cmd = [nvcc, "-shared", "-cudart", "static", "-o", LIB + ".tmp"] + objs + ["-lpthread"]
+    cmd = [nvcc, "-shared", "-cudart", "static", "-Wno-deprecated-gpu-targets", "-o", LIB + ".tmp"] + objs + ["-lpthread"]
     subprocess.check_call(cmd)
     os.replace(LIB + ".tmp", LIB)
     return LIB

@@ -24,8 +24,13 @@ namespace {
 
 constexpr int F6T = 256;
 #ifndef F6_MINB
-#define F6_MINB 6
+#define F6_MINB 8        // 32 registers (a few spills in the parse path) and 64 resident warps: 0.653 -> 0.631 ms vs 6 CTAs at 40
 #endif
+// shared memory of a CTA: window | newline bitmap | line-end list | misc (no candidate bitmap: 24.4 KiB, 8 CTAs / SM)
+constexpr int F6_OFF_BM = F3_OFF_BM;
+constexpr int F6_OFF_POS = F6_OFF_BM + F2_WORDS * 8;            // u16[F3_PCAP]
+constexpr int F6_OFF_MISC = F6_OFF_POS + F3_PCAP * 2;
+constexpr int F6_SMEM = F6_OFF_MISC + 128;
 constexpr uint32_t F6_BLANK = 1u << 25;        // scratch digest: the header had no name token
 
 // ---- record parser without the candidate bitmap ------------------------------------------------------------
@@ -152,10 +157,10 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
     extern __shared__ __align__(128) uint8_t f6_smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t sm0 = smem_u32(f6_smem);
-    const u64 *s_bm = reinterpret_cast<const u64 *>(f6_smem + F3_OFF_BM);
-    uint16_t *s_pos = reinterpret_cast<uint16_t *>(f6_smem + F3_OFF_POS);
-    uint32_t *s_misc = reinterpret_cast<uint32_t *>(f6_smem + F3_OFF_MISC);
-    const uint32_t s_bar = sm0 + F3_OFF_MISC + 64, a_pos = sm0 + F3_OFF_POS;
+    const u64 *s_bm = reinterpret_cast<const u64 *>(f6_smem + F6_OFF_BM);
+    uint16_t *s_pos = reinterpret_cast<uint16_t *>(f6_smem + F6_OFF_POS);
+    uint32_t *s_misc = reinterpret_cast<uint32_t *>(f6_smem + F6_OFF_MISC);
+    const uint32_t s_bar = sm0 + F6_OFF_MISC + 64, a_pos = sm0 + F6_OFF_POS;
     BatchState *S = b.state;
     const uint32_t n_todo = REDO ? min(S->n_redo, b.redo_cap) : total_tiles;
 
@@ -242,7 +247,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
                     const uint32_t c = (uint32_t)tid + (uint32_t)F6T * i;
                     if (i == 4 && tid >= F2_HALO / 16) break;   // halo: 128 chunks, warps 0-3
                     const uint4 q = lds128(sm0 + 16u * c);
-                    sts16(sm0 + F3_OFF_BM + 2u * c,
+                    sts16(sm0 + F6_OFF_BM + 2u * c,
                           f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w)));
                 }
             } else {
@@ -255,7 +260,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
                     const uint32_t keep = off >= T.win ? 0u : (T.win - off >= 16u ? 0xffffu : (1u << (T.win - off)) - 1u);
                     m &= keep;
                     if ((vbit >> 4) == c && f2_byte(T, T.n - 1u) != '\n') m |= 1u << (vbit & 15u);   // no final '\n'
-                    sts16(sm0 + F3_OFF_BM + 2u * c, m);
+                    sts16(sm0 + F6_OFF_BM + 2u * c, m);
                 }
             }
         }

@@ -78,14 +78,14 @@ void launch_frame2(const BatchDev &b, cudaStream_t s)
     if (g_frame_variant == 10) {                               // k_frame6: independent tiles, scan + densify after
         static int occ6 = 0;
         if (!occ6) {
-            cudaFuncSetAttribute(k_frame6<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
-            cudaFuncSetAttribute(k_frame6<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F3_SMEM);
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ6, k_frame6<false>, F6T, F3_SMEM);
+            cudaFuncSetAttribute(k_frame6<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F6_SMEM);
+            cudaFuncSetAttribute(k_frame6<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)F6_SMEM);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ6, k_frame6<false>, F6T, F6_SMEM);
             if (occ6 < 1) occ6 = 1;
         }
         uint32_t g6 = (uint32_t)(g_sms * (g_f6_ctas > 0 && g_f6_ctas < occ6 ? g_f6_ctas : occ6));
         if (g6 > total) g6 = total;
-        k_frame6<false><<<g6, F6T, F3_SMEM, s>>>(b, total);
+        k_frame6<false><<<g6, F6T, F6_SMEM, s>>>(b, total);
         return;
     }
     if (g_frame_variant >= 7 && g_frame_variant <= 9) {        // k_frame5: scan / look-back / parse warps
@@ -157,7 +157,7 @@ void launch_fix(const BatchDev &b, cudaStream_t s)
             for (int i = 0; i < b.n_streams; ++i) max_tiles = max(max_tiles, b.st[i].n ? b.st[i].n / (uint32_t)F2_TILE + 1u : 0u);
             k_tilescan<<<dim3((max_tiles + kTileChunk - 1) / kTileChunk, b.n_streams), kTileChunk, 0, s>>>(b);
             k_densify<<<(uint32_t)g_sms * 4u, 256, 0, s>>>(b, total);
-            k_frame6<true><<<(uint32_t)g_sms, F6T, F3_SMEM, s>>>(b, total);
+            k_frame6<true><<<(uint32_t)g_sms, F6T, F6_SMEM, s>>>(b, total);
         }
     }
     const uint32_t gx = (uint32_t)max(1, g_sms * 4 / b.n_streams);
