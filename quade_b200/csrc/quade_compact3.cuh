@@ -23,8 +23,14 @@ namespace {
 constexpr int C3_TP = kCompactTilePairs;                  // pairs per tile (upper bound; the batch's value is in BatchState)
 static_assert(C3_TP >= 1 && C3_TP <= 8, "k_compact3: one record lane per read of the tile, 16 record lanes");
 constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stream per stage
-constexpr int C3_HS = 176;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
-constexpr int C3_SUFV = 4;                // staged suffix: up to 64 bytes per pair
+#ifndef QUADE_C3_HS
+#define QUADE_C3_HS 176
+#endif
+#ifndef QUADE_C3_SUFV
+#define QUADE_C3_SUFV 4
+#endif
+constexpr int C3_HS = QUADE_C3_HS;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
+constexpr int C3_SUFV = QUADE_C3_SUFV;                // staged suffix: up to 64 bytes per pair
 constexpr int C3_STAGES = 1;               // 1: more resident warps hide the copy latency; 2: per-warp prefetch
 constexpr int C3_IN_BYTES = C3_STAGES * 2 * (C3_CAP + 32);
 constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * 32 + 32;

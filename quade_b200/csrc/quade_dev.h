@@ -28,6 +28,9 @@ constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
 #ifndef QUADE_C3_CAP
 #define QUADE_C3_CAP 3072
 #endif
+#ifndef QUADE_C3_MARGIN
+#define QUADE_C3_MARGIN 8         /* the staged span of a tile is sized for mean record size * (1 + 1/MARGIN) */
+#endif
 constexpr int kCompactTilePairs = QUADE_C3_TP;   // k_compact3: pairs per tile (upper bound) ...
 constexpr int kCompactStageBytes = QUADE_C3_CAP; // ... and staged bytes per read stream and tile
 constexpr int kTileChunk = 1024;   // k_frame6 / k_tilescan: tiles per chunk of the tile table (16 MiB of input)

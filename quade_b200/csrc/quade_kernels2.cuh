@@ -110,7 +110,7 @@ __global__ void k_pairing(const __grid_constant__ BatchDev b)
     uint32_t tp = kCompactTilePairs;
     if (np > 0) {
         uint32_t avg = max(S->consumed[0], S->consumed[1]) / np + 1u;
-        avg += avg / 8u;
+        avg += avg / (uint32_t)QUADE_C3_MARGIN;
         tp = ((uint32_t)kCompactStageBytes - 48u) / avg;
         tp = tp > (uint32_t)kCompactTilePairs ? (uint32_t)kCompactTilePairs : (tp < 1u ? 1u : tp);
     }
