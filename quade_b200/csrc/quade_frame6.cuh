@@ -498,7 +498,10 @@ __global__ void __launch_bounds__(kTileChunk) k_tilescan(const __grid_constant__
 // k_densify: one warp per tile, scratch -> dense per-record arrays at the true record index (the pairing ordinal
 // of a file without invalid records).  Counts the records with len(seq) != len(qual), finds the first blank header.
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 4) k_densify(const __grid_constant__ BatchDev b, uint32_t total_tiles)
+#ifndef F6_DENSIFY_MINB
+#define F6_DENSIFY_MINB 3   // 80 registers, no spills: 2 / 3 / 4 / 6 / 8 CTAs per SM measured 0.179 / 0.142 / 0.148 / 0.155 / 0.188 ms for the stage
+#endif
+__global__ void __launch_bounds__(256, F6_DENSIFY_MINB) k_densify(const __grid_constant__ BatchDev b, uint32_t total_tiles)
 {
     const int lane = threadIdx.x & 31;
     BatchState *S = b.state;

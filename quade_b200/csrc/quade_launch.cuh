@@ -156,7 +156,7 @@ void launch_fix(const BatchDev &b, cudaStream_t s)
             uint32_t max_tiles = 0;
             for (int i = 0; i < b.n_streams; ++i) max_tiles = max(max_tiles, b.st[i].n ? b.st[i].n / (uint32_t)F2_TILE + 1u : 0u);
             k_tilescan<<<dim3((max_tiles + kTileChunk - 1) / kTileChunk, b.n_streams), kTileChunk, 0, s>>>(b);
-            k_densify<<<(uint32_t)g_sms * 4u, 256, 0, s>>>(b, total);
+            k_densify<<<(uint32_t)g_sms * (uint32_t)F6_DENSIFY_MINB, 256, 0, s>>>(b, total);
             k_frame6<true><<<(uint32_t)g_sms, F6T, F6_SMEM, s>>>(b, total);
         }
     }
