@@ -300,3 +300,34 @@ def test_full_size_batch_matches_oracle_and_is_split_invariant(name):
     assert total == n and (csum == counters).all()
     assert [[x.digest() for x in row] for row in h] == one_shot
     ctx.close()
+
+
+@pytest.mark.parametrize("max_len", [3000, 40000])
+def test_long_reads_spanning_tiles_match_oracle(max_len):
+    """Insert reads far longer than Illumina's: records larger than the 2 KiB halo of a framing tile and (40000)
+    larger than a whole 16 KiB tile, so that a record's four lines lie in different tiles; long names and
+    descriptions; index reads stay short.  Same bytes as the oracle, whatever path the tiles take."""
+    rng = np.random.default_rng(max_len)
+    n = 400
+    keys = ["ACGTACGT", "TTGCAAGC", "GGATCCAA"]
+    p = O.OracleParams(False, [(0, 8), (0, 0), (0, 0), (0, 0)], 20, keys)
+    bases = np.frombuffer(b"ACGTN", dtype=np.uint8)
+    r1, r2, i1 = [], [], []
+    for j in range(n):
+        name = b"read%d/%s" % (j, b"x" * int(rng.integers(0, 120)))
+        for out in (r1, r2):
+            L = int(rng.integers(1, max_len))
+            seq = bases[rng.integers(0, 5, L)].tobytes()
+            qual = (rng.integers(33, 74, L).astype(np.uint8)).tobytes()
+            out.append(b"@" + name + b" desc " + b"d" * int(rng.integers(0, 60)) + b"\n" + seq + b"\n+" +
+                       (name if j % 7 == 0 else b"") + b"\n" + qual + b"\n")
+        idx = keys[j % 3].encode() if j % 4 else bases[rng.integers(0, 4, 8)].tobytes()
+        iq = (rng.integers(33 + 15, 74, 8).astype(np.uint8)).tobytes()
+        i1.append(b"@" + name + b"\n" + idx + b"\n+\n" + iq + b"\n")
+    streams = [b"".join(r1), b"".join(r2), b"".join(i1)]
+    ref = O.demux_batch(p, streams, last=True)
+    ctx, _ = _ctx_for(p, max_stream_bytes=max(len(x) for x in streams) + 4096, max_pairs=n + 16)
+    r = ctx.run(streams, last=True)
+    _assert_same(r, ref, p.nbins, "long reads %d" % max_len)
+    assert r.n_pairs == n
+    ctx.close()
