@@ -60,7 +60,7 @@ struct quade_ctx {
     uint64_t cap_bytes = 0, cap_pairs = 0, cap_rec = 0;
     uint32_t suf_cap = 4, pairs_per_block = 4096, cap_blocks = 1;
     uint64_t out_cap = 0;
-    cudaStream_t s_copy = nullptr, s_compute = nullptr, s_d2h = nullptr, s_back = nullptr;
+    cudaStream_t s_copy = nullptr, s_compute = nullptr, s_d2h = nullptr, s_back = nullptr, s_meta = nullptr;
     bool overlap = false;                // k_compact3 of batch i on s_back beside the framing of batch i + 1
     std::vector<Slot> slots;
     int head = 0, tail = 0, in_flight = 0;
@@ -306,7 +306,8 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     if (cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_d2h, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->s_back, cudaStreamNonBlocking) != cudaSuccess)
+        cudaStreamCreateWithFlags(&c->s_back, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->s_meta, cudaStreamNonBlocking) != cudaSuccess)
         rc = fail(QUADE_ERR_CUDA, "cudaStreamCreate failed");
     c->slots.resize(c->n_slots);
     for (int i = 0; i < c->n_slots && rc == QUADE_OK; ++i) rc = slot_alloc(c, c->slots[i]);
@@ -333,6 +334,7 @@ extern "C" int quade_ctx_destroy(quade_ctx *c)
     if (c->s_compute) cudaStreamDestroy(c->s_compute);
     if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
     if (c->s_back) cudaStreamDestroy(c->s_back);
+    if (c->s_meta) cudaStreamDestroy(c->s_meta);
     delete c;
     return QUADE_OK;
 }
