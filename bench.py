@@ -231,7 +231,8 @@ def run_ours(args, rank, world, local_rank):
     # code path on a fresh box pages in library text and loads CUDA modules lazily: tens of ms)
     t_spin = time.perf_counter()
     while (time.perf_counter() - t_spin) * 1e3 < args.spinup_ms:
-        timed_block(4)
+        device_steps(4)                    # no collective here: the number of rounds is wall-clock bound per rank
+    barrier()
     timed_block(args.warmup)
     barrier()
     sampler.begin()
