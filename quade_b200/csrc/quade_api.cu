@@ -1,5 +1,5 @@
 // quade_api.cu -- the C-ABI of libquade_b200.so (include/quade_b200.h): contexts, batch slots, the four-stream
-// pipeline (H2D copy | kernels | D2H copy) and the host-side perfect-hash builder for the sample registry.
+// pipeline (H2D copy | kernels | small per-batch results | D2H copy) and the host-side perfect-hash builder for the sample registry.
 #include "quade_dev.h"
 #include "../../include/quade_b200.h"
 
