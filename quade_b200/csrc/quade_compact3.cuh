@@ -101,12 +101,23 @@ struct TileMeta {
     bool staged;                  // uniform: the spans fit the stage
 };
 
-__global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDev b)
+// C3_WPC independent warps per CTA, each with its own C3_SMEM bytes and tiles: the 1 KiB of shared memory the
+// system reserves per CTA is paid once per C3_WPC warps (1 -> 20 warps per SM, 11 -> 22)
+#ifndef QUADE_C3_WPC
+#define QUADE_C3_WPC 22        // measured: 1 / 3 / 11 / 22 warps per CTA = 0.674 / 0.704 / 0.662 / 0.658 ms
+#endif
+constexpr int C3_WPC = QUADE_C3_WPC;
+static_assert(C3_SMEM % 16 == 0, "per-warp shared memory regions stay 16-byte aligned (bulk copies, 128-bit accesses)");
+
+__global__ void __launch_bounds__(32 * C3_WPC) k_compact3(const __grid_constant__ BatchDev b)
 {
-    extern __shared__ __align__(128) uint8_t c3_smem[];
+    extern __shared__ __align__(128) uint8_t c3_smem_all[];
     const BatchState *St = b.state;
     if (St->err_capacity) return;
-    const int lane = threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp_in_cta = threadIdx.x >> 5;
+    uint8_t *c3_smem = c3_smem_all + warp_in_cta * (uint32_t)C3_SMEM;
+    const uint32_t first_tile = blockIdx.x * (uint32_t)C3_WPC + warp_in_cta, tile_stride = gridDim.x * (uint32_t)C3_WPC;
     const uint32_t n_pairs = St->n_pairs;
     uint32_t tp = St->compact_tp;
     tp = tp < 1u ? 1u : (tp > (uint32_t)C3_TP ? (uint32_t)C3_TP : tp);
@@ -188,7 +199,7 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
     };
 
     uint32_t phase_bits = 0;
-    uint32_t tile = blockIdx.x, it = 0;
+    uint32_t tile = first_tile, it = 0;
     TileMeta cur, nxt;
     if (tile < n_tiles) {
         load_raw(tile, cur);
@@ -196,9 +207,9 @@ __global__ void __launch_bounds__(32) k_compact3(const __grid_constant__ BatchDe
         issue(cur, 0);
     }
 #pragma unroll 1
-    for (; tile < n_tiles; tile += gridDim.x, ++it) {
+    for (; tile < n_tiles; tile += tile_stride, ++it) {
         const uint32_t stage = C3_STAGES == 2 ? (it & 1u) : 0u;
-        const uint32_t ntile = tile + gridDim.x;
+        const uint32_t ntile = tile + tile_stride;
         load_raw(ntile, nxt);                                          // loads only; consumed at the end of the iteration
         if (C3_STAGES == 2 && ntile < n_tiles) {
             finish_meta(nxt);

@@ -35,8 +35,8 @@ static void init_launch_config()
     if (g_occ_frame3 < 1) g_occ_frame3 = 1;
     if (g_occ_validate < 1) g_occ_validate = 1;
     if (g_occ_compact < 1) g_occ_compact = 1;
-    cudaFuncSetAttribute(k_compact3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C3_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact3, k_compact3, 32, C3_SMEM);
+    cudaFuncSetAttribute(k_compact3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C3_SMEM * C3_WPC));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact3, k_compact3, 32 * C3_WPC, C3_SMEM * C3_WPC);
     if (g_occ_compact3 < 1) g_occ_compact3 = 1;
 }
 
@@ -241,7 +241,7 @@ void launch_compact(const BatchDev &b, cudaStream_t s)
         uint32_t grid3 = (uint32_t)(g_sms * (g_c3_ctas > 0 && g_c3_ctas < g_occ_compact3 ? g_c3_ctas : g_occ_compact3));
         if (grid3 > b.cap_pairs) grid3 = b.cap_pairs;
         if (grid3 < 1) grid3 = 1;
-        k_compact3<<<grid3, 32, C3_SMEM, s>>>(b);
+        k_compact3<<<grid3, 32 * C3_WPC, C3_SMEM * C3_WPC, s>>>(b);
         return;
     }
     uint32_t grid = (uint32_t)(g_sms * g_occ_compact);
