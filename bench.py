@@ -268,7 +268,8 @@ def run_ours(args, rank, world, local_rank):
     roofline = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": ncu_traffic(kname), "peak_source": peak_src, "algorithmic_bytes_per_launch": alg[dom],
                 "ms_per_launch": kms[dom],
-                "per_kernel": {k: {"ms": kms[k], "GB/s": (alg[k] / (kms[k] * 1e-3) / 1e9) if k in alg else None} for k in kms},
+                "per_kernel": {k: {"ms": kms[k], "GB/s": (alg[k] / (kms[k] * 1e-3) / 1e9) if k in alg else None,
+                                   "frac": (alg[k] / (kms[k] * 1e-3) / 1e9 / peak) if k in alg else None} for k in kms},
                 "pipeline": {"algorithmic_bytes_per_step": in_bytes + out_bytes,
                              "achieved": (in_bytes + out_bytes) * args.steps / (ms_total * 1e-3) / 1e9,
                              "frac": (in_bytes + out_bytes) * args.steps / (ms_total * 1e-3) / 1e9 / peak}}

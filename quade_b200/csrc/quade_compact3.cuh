@@ -24,7 +24,7 @@ constexpr int C3_TP = kCompactTilePairs;                  // pairs per tile (upp
 static_assert(C3_TP >= 1 && C3_TP <= 8, "k_compact3: one record lane per read of the tile, 16 record lanes");
 constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stream per stage
 #ifndef QUADE_C3_HS
-#define QUADE_C3_HS 176
+#define QUADE_C3_HS 144         /* name + suffix up to 98 bytes always take the fast path (176: 130); longer ones the generic one */
 #endif
 #ifndef QUADE_C3_SUFV
 #define QUADE_C3_SUFV 4
@@ -102,9 +102,9 @@ struct TileMeta {
 };
 
 // C3_WPC independent warps per CTA, each with its own C3_SMEM bytes and tiles: the 1 KiB of shared memory the
-// system reserves per CTA is paid once per C3_WPC warps (1 -> 20 warps per SM, 11 -> 22)
+// system reserves per CTA is paid once per C3_WPC warps (with the 144-byte HEAD slots: 24 warps of 9568 bytes in one CTA per SM)
 #ifndef QUADE_C3_WPC
-#define QUADE_C3_WPC 22        // measured: 1 / 3 / 11 / 22 warps per CTA = 0.674 / 0.704 / 0.662 / 0.658 ms
+#define QUADE_C3_WPC 24        // 6 warps per scheduler; measured 20 (1 per CTA) / 22 / 23 / 24 warps per SM = 0.674 / 0.656 / 0.62 / 0.601 ms
 #endif
 constexpr int C3_WPC = QUADE_C3_WPC;
 static_assert(C3_SMEM % 16 == 0, "per-warp shared memory regions stay 16-byte aligned (bulk copies, 128-bit accesses)");
