@@ -26,7 +26,10 @@ class FastqReader:
     def __init__(self, fastq_file, prefetch=True, depth=4):
         self.path = fastq_file
         # same rule as the reference: FastqReader.py:30
-        self._fh = gzip.open(fastq_file, "rb") if fastq_file[-2:] == "gz" else open(fastq_file, "rb", buffering=0)
+        self._plain = fastq_file[-2:] != "gz"
+        self._fh = open(fastq_file, "rb", buffering=0) if self._plain else gzip.open(fastq_file, "rb")
+        if self._plain:
+            prefetch = False       # plain files are read straight into the caller's (pinned) buffer: no copy to hide
         self.eof = False
         self.bytes_read = 0
         self._pending = None       # (memoryview, offset) of a block partly handed out
@@ -58,6 +61,16 @@ class FastqReader:
         """Fill `arr` (numpy uint8, C-contiguous) as far as the file allows; returns bytes written."""
         want = int(arr.size)
         done = 0
+        if self._plain:
+            mv = memoryview(arr)
+            while done < want:
+                n = self._fh.readinto(mv[done:])
+                if not n:
+                    self.eof = True
+                    break
+                done += n
+            self.bytes_read += done
+            return done
         while done < want and not self.eof:
             if self._pending is None:
                 blk = self._next_block()

@@ -78,6 +78,29 @@ def test_golden_run_through_the_host_loop(tmp_path, monkeypatch, batch_bytes):
     _check_golden_outputs(wd)
 
 
+@pytest.mark.parametrize("batch_bytes", [1 << 20, 1499])
+def test_golden_run_with_plain_text_inputs(tmp_path, monkeypatch, batch_bytes):
+    """Same run with the inputs decompressed to `.fastq` files: a path that does not end in "gz" is opened as a plain
+    file (FastqReader.py:30) and read straight into the staging buffers."""
+    from quade_b200.quade import Quade
+    _fresh()
+    wd = _stage_dataset(tmp_path)
+    for f in sorted(os.listdir(tmp_path / "dataset")):
+        if f.endswith(".fastq.gz"):
+            with gzip.open(tmp_path / "dataset" / f, "rb") as src, open(tmp_path / "dataset" / f[:-3], "wb") as dst:
+                dst.write(src.read())
+            os.remove(tmp_path / "dataset" / f)
+    conf = (wd / "Quade_conf_file.txt").read_text().replace(".fastq.gz", ".fastq")
+    (wd / "Quade_conf_file.txt").write_text(conf)
+    monkeypatch.chdir(wd)
+    monkeypatch.setattr(Quade, "ENGINE_FACTORY", util.OracleEngine)
+    monkeypatch.setattr(Quade, "BATCH_BYTES", batch_bytes)
+    q = Quade(conf_file="Quade_conf_file.txt")
+    assert all(f.endswith(".fastq") for f in q.seq_R1 + q.seq_R2 + q.index_R1 + q.index_R2)
+    assert q() == 0
+    _check_golden_outputs(wd)
+
+
 def test_config_errors_exit_1(tmp_path, monkeypatch, capsys):
     from quade_b200.quade import Quade
     wd = _stage_dataset(tmp_path)
