@@ -321,17 +321,22 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
             uint32_t i = before + inc - cnt;
             uint32_t lo = (uint32_t)mine, hi = (uint32_t)(mine >> 32);
             const uint32_t o0 = (uint32_t)tid * 64u;
-            while (lo) {
-                const uint32_t bit = (uint32_t)__ffs((int)lo) - 1u;
-                lo &= lo - 1u;
-                if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(o0 + bit);
-                ++i;
-            }
-            while (hi) {
-                const uint32_t bit = (uint32_t)__ffs((int)hi) - 1u;
-                hi &= hi - 1u;
-                if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(o0 + 32u + bit);
-                ++i;
+            // both halves of the word advance in the same iteration: the warp loops max(popc(lo), popc(hi)) times
+            // over its lanes instead of max popc(lo) + max popc(hi)
+            uint32_t ih = i + (uint32_t)__popc(lo);
+            while (lo | hi) {
+                if (lo) {
+                    const uint32_t bit = (uint32_t)__ffs((int)lo) - 1u;
+                    lo &= lo - 1u;
+                    if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(o0 + bit);
+                    ++i;
+                }
+                if (hi) {
+                    const uint32_t bit = (uint32_t)__ffs((int)hi) - 1u;
+                    hi &= hi - 1u;
+                    if (ih < (uint32_t)F3_PCAP) s_pos[ih] = (uint16_t)(o0 + 32u + bit);
+                    ++ih;
+                }
             }
             if (warp == 1) {
                 i = total + hinc - hcnt;
