@@ -8,8 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("QUADE_LIB_PATH") or os.path.join(HERE, "libquade_b200.so")   # override: A/B builds of kernel variants
 SOURCES = ["quade_kernels.cu", "quade_api.cu", "quade_synth.cpp"]
-DEPS = SOURCES + ["quade_dev.h", "quade_kernels2.cuh", "quade_kernels3.cuh", "quade_compact.cuh", "quade_compact2.cuh", "quade_compact3.cuh", "quade_ptx.cuh", "quade_frame2.cuh", "quade_frame3.cuh", "quade_frame4.cuh", "quade_frame5.cuh", "quade_frame6.cuh", "quade_launch.cuh", "quade_api2.inc",
-                  os.path.join("..", "..", "include", "quade_b200.h")]
+DEPS = SOURCES + sorted(f for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inc"))) + [os.path.join("..", "..", "include", "quade_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-O3,-Wall", "-cudart", "static"]
 

@@ -106,28 +106,22 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
 {
     const int ns = c->n_streams, nb = c->n_bins;
     const size_t cap_rec = c->cap_rec, cap_pairs = c->cap_pairs;
-    const size_t frame_tiles = c->cap_bytes / kFrameTileMin + 2, val_tiles = cap_rec / kValidateTile + 2;
+    const size_t val_tiles = cap_rec / kValidateTile + 2;
     // sizes
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
-    size_t o_in[4], o_nl[4], o_e1[4], o_e3[4], o_noff[4], o_nlen[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sf[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4], o_rec_t[4], o_vnlen_t[4], o_vend_t[4], o_dig_t[4], o_sfx_t[4], o_tt[4];
+    size_t o_in[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4], o_rec_t[4], o_vnlen_t[4], o_vend_t[4], o_dig_t[4], o_sfx_t[4], o_tt[4];
     uint32_t sfx_slot[4] = {0, 0, 0, 0};
     const size_t o_zero = take(0);
     const size_t o_state = take(sizeof(BatchState));
     const size_t o_counters = take((size_t)nb * 8);
     for (int s = 0; s < ns; ++s) {
-        o_sf[s] = take(frame_tiles * 8);
-        o_sv[s] = take((val_tiles > frame_tiles ? val_tiles : frame_tiles) * 8);
+        o_sv[s] = take(val_tiles * 8);
     }
     const size_t zero_end = off;
     for (int s = 0; s < ns; ++s) {
         o_tt[s] = take((c->cap_bytes / kFrameTile + 2) * 16);
         o_in[s] = take(c->cap_bytes + 256);
-        o_nl[s] = take(cap_rec * 16);
-        o_e1[s] = take(cap_rec * 4);
-        o_e3[s] = take(cap_rec * 4);
-        o_noff[s] = take(cap_rec * 4);
-        o_nlen[s] = take(cap_rec * 4);
         o_rec[s] = take(cap_rec * 16);
         o_vnlen[s] = take(cap_rec * 4);
         o_vrec[s] = take(cap_rec * 4);
@@ -188,11 +182,6 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         sl.d_in[s] = A + o_in[s];
         st.data = sl.d_in[s];
         st.cap_rec = (uint32_t)cap_rec;
-        st.nl = reinterpret_cast<uint32_t *>(A + o_nl[s]);
-        st.e1 = reinterpret_cast<uint32_t *>(A + o_e1[s]);
-        st.e3 = reinterpret_cast<uint32_t *>(A + o_e3[s]);
-        st.noff = reinterpret_cast<uint32_t *>(A + o_noff[s]);
-        st.nlen = reinterpret_cast<uint32_t *>(A + o_nlen[s]);
         st.rec = reinterpret_cast<uint4 *>(A + o_rec[s]);
         st.vnlen = reinterpret_cast<uint32_t *>(A + o_vnlen[s]);
         st.vrec = reinterpret_cast<uint32_t *>(A + o_vrec[s]);
@@ -207,7 +196,6 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         st.sfx_slot = sfx_slot[s];
         st.wi = s >= 2 ? (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]) : 0u;
         st.wm = s >= 2 ? (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]) : 0u;
-        st.status_frame = reinterpret_cast<unsigned long long *>(A + o_sf[s]);
         st.status_validate = reinterpret_cast<unsigned long long *>(A + o_sv[s]);
         st.tile_tab = reinterpret_cast<uint4 *>(A + o_tt[s]);
     }
@@ -299,8 +287,6 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->pairs_per_block = ppb;
     c->cap_blocks = (uint32_t)((c->cap_pairs + ppb - 1) / ppb);
     c->cumulative.assign(c->n_bins, 0);
-    if (const char *v = getenv("QUADE_COMPACT")) set_compact_variant(atoi(v));
-    if (const char *v = getenv("QUADE_FRAME")) set_frame_variant(atoi(v));
     if (const char *v = getenv("QUADE_OVERLAP")) c->overlap = atoi(v) != 0 && c->n_slots >= 2;
     int rc = QUADE_OK;
     if (cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking) != cudaSuccess ||

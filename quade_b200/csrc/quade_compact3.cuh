@@ -80,6 +80,21 @@ __device__ __forceinline__ void emit_generic(const BatchDev &b, int k, uint32_t 
     }
 }
 
+// 16 bytes starting at byte r (0..15) of the 32 bytes {A,B}; r is warp-uniform
+__device__ __forceinline__ uint4 shift_bytes(const uint4 A, const uint4 B, uint32_t r)
+{
+    const uint32_t sh = (r & 3u) * 8u;
+    uint32_t w0, w1, w2, w3, w4;
+    switch (r >> 2) {
+    case 0: w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; break;
+    case 1: w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; break;
+    case 2: w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; break;
+    default: w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; break;
+    }
+    return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
+                      __funnelshift_r(w3, w4, sh));
+}
+
 // 16 bytes starting at byte r (0..15) of the 32 bytes {A,B}; r is warp-uniform.  Two levels of uniform selects
 // (r & 4, r & 8) pick the five source words, four funnel shifts align them: 16 instructions, no branch
 __device__ __forceinline__ uint4 shift_bytes_sel(const uint4 A, const uint4 B, uint32_t r)

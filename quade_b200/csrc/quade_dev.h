@@ -3,9 +3,6 @@
 // HBM layout of one batch slot (all offsets are u32: a stream batch is < 3.75 GiB)
 //   per stream s (R1, R2, I1[, I2]):
 //     data[n]                     the raw FASTQ bytes (16-byte aligned base)
-//     nl[4*cap_rec]               position of every '\n' (line k ends at nl[k]); record j = lines 4j..4j+3
-//     e1[cap_rec], e3[cap_rec]    rstripped end of the sequence / quality line of record j
-//     noff[cap_rec], nlen[cap_rec] name token of record j (FastqReader.py:42)
 //     rec[cap_rec] (uint4)        per VALID record, compacted: {name_off, seq_off, qual_off, seq_len}
 //     vnlen[cap_rec], vrec[cap_rec] name_len and record index of the v-th valid record
 //   per pair p:
@@ -61,8 +58,6 @@ struct StreamDev {
     const uint8_t *data;
     uint32_t n;
     uint32_t cap_rec;
-    uint32_t *nl;
-    uint32_t *e1, *e3, *noff, *nlen;
     uint4 *rec;
     uint32_t *vnlen, *vrec;
     // k_frame2 (fused frame + validate + index digest)
@@ -73,7 +68,6 @@ struct StreamDev {
     uint32_t *vnlen_t, *vend_t;
     uint8_t *sfx_t;
     uint32_t sfx_slot, wi, wm;           // slot bytes (multiple of 16), widths of the index / molecular spans
-    unsigned long long *status_frame;    // decoupled look-back words, one per 16 KiB tile
     unsigned long long *status_validate; // one per 1024-record tile
     uint4 *tile_tab;                     // k_frame6: per 16 KiB tile {line ends | k0, guess | ok, records, scratch base}
 };
@@ -133,27 +127,16 @@ __host__ __device__ inline uint32_t key_slot(uint64_t h, uint32_t disp, uint32_t
 }
 
 // launchers (quade_kernels.cu).  All enqueue on `s`; sizes unknown to the host are read from BatchState.
-void launch_frame(const BatchDev &b, cudaStream_t s);
-void launch_frame2(const BatchDev &b, cudaStream_t s);
-int frame_launches();     // kernels launch_frame2 enqueues for the current variant
-void launch_fix(const BatchDev &b, cudaStream_t s);
+void launch_frame(const BatchDev &b, cudaStream_t s);      // k_frame6
+void launch_fix(const BatchDev &b, cudaStream_t s);        // k_tilescan, k_densify, k_frame6<redo>, k_fix_compact, k_fix_copyback
 void launch_pairing2(const BatchDev &b, cudaStream_t s);
 void launch_classify2(const BatchDev &b, cudaStream_t s);
-void set_frame_variant(int v);
-int frame_variant();     // 10 = k_frame6 + k_tilescan + k_densify (default), 2..9 = look-back variants, 1 = k_frame/k_validate/k_classify
-void launch_validate(const BatchDev &b, cudaStream_t s);
-void launch_pairing(const BatchDev &b, cudaStream_t s);
-void launch_classify(const BatchDev &b, cudaStream_t s);
-void launch_binscan(const BatchDev &b, cudaStream_t s);
+void launch_binscan(const BatchDev &b, cudaStream_t s);    // k_binscan_blocks, k_binscan_bins
 void launch_offsets(const BatchDev &b, cudaStream_t s);
-void launch_compact(const BatchDev &b, cudaStream_t s);
-void set_compact_variant(int v);   // 3 = TMA-staged k_compact3 (default), 2 = cp.async k_compact
-int kernel_launch_count(int stage);
+void launch_compact(const BatchDev &b, cudaStream_t s);    // k_compact3
 size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
 
-constexpr int kFrameTile = 16384;   // bytes per frame tile (k_frame, k_frame2, k_frame3)
-constexpr int kFrameTileMin = 8192; // smallest tile of any frame kernel (sizes the look-back status arrays)
-constexpr int kFrameHalo = 256;
+constexpr int kFrameTile = 16384;   // bytes per frame tile (k_frame6)
 constexpr int kValidateTile = 1024; // records per validate tile
 
 } // namespace quade

@@ -71,88 +71,10 @@ __device__ __forceinline__ uint32_t f2_next_nl(const F2Tile &t, uint32_t from)
     return (t.last && t.n > 0u && from <= t.n && t.data[t.n - 1u] != '\n') ? t.n : F2_NONE;
 }
 
-// is the byte at global position pos <= 0x20 ?
-__device__ __forceinline__ bool f2_cand(const F2Tile &t, uint32_t pos)
-{
-    const uint32_t q = pos - t.tbase;
-    return q < t.win ? ((t.bc[q >> 6] >> (q & 63u)) & 1ull) != 0ull : t.data[pos] <= 0x20u;
-}
-// first position in [from, e) whose byte is <= 0x20, e if none
-__device__ __forceinline__ uint32_t f2_next_cand(const F2Tile &t, uint32_t from, uint32_t e)
-{
-    uint32_t q = from - t.tbase;
-    if (q < t.cap) {
-        uint32_t w = q >> 6;
-        u64 m = t.bc[w] & (~0ull << (q & 63u));
-        for (;;) {
-            if (m) {
-                const uint32_t p = t.tbase + w * 64u + (uint32_t)__ffsll((long long)m) - 1u;
-                return p < e ? p : e;
-            }
-            if (++w >= (t.cap >> 6) || t.tbase + w * 64u >= e) break;
-            m = t.bc[w];
-        }
-        from = t.tbase + t.cap;
-    }
-    for (u64 p = from; p < e; ++p)
-        if (t.data[p] <= 0x20u) return (uint32_t)p;
-    return e;
-}
-
-// end of line.rstrip() for the line [s, e) whose terminator sits at e (Python-2 str whitespace)
-__device__ __forceinline__ uint32_t f2_rstrip(const F2Tile &t, uint32_t s, uint32_t e)
-{
-    if (e > s && f2_cand(t, e - 1u))
-        while (e > s && is_ws(f2_byte(t, e - 1u))) --e;
-    return e;
-}
-
-// first position in [p, e) holding whitespace, e if none: hop over the candidate bytes
-__device__ __forceinline__ uint32_t f2_find_ws(const F2Tile &t, uint32_t p, uint32_t e)
-{
-    for (;;) {
-        const uint32_t c = f2_next_cand(t, p, e);
-        if (c >= e) return e;
-        if (is_ws(f2_byte(t, c))) return c;
-        p = c + 1u;                                           // a control character inside the token
-    }
-}
-
 struct F2Rec {
     uint32_t name_off, nlen, seq_off, qual_off, seq_len, end;   // end: position after the record's last line
     bool complete, valid;
 };
-
-// one record starting at global position hs (FastqReader.py:37-44, FastqSeq.py:55).  pos[li .. li+3] are the
-// window offsets of its four line ends as far as the list (npos entries) reaches; the rest is searched.
-__device__ __forceinline__ F2Rec f2_parse(const F2Tile &t, uint32_t hs, const uint16_t *pos, uint32_t li, uint32_t npos)
-{
-    F2Rec r;
-    r.complete = r.valid = false;
-    r.name_off = r.nlen = r.seq_off = r.qual_off = r.seq_len = r.end = 0u;
-    if (hs > t.n) return r;
-    const uint32_t nl0 = li < npos ? t.tbase + pos[li] : f2_next_nl(t, hs);
-    if (nl0 == F2_NONE || nl0 >= t.n) return r;           // a line ending at n is the file's last line
-    const uint32_t nl1 = li + 1u < npos ? t.tbase + pos[li + 1u] : f2_next_nl(t, nl0 + 1u);
-    if (nl1 == F2_NONE || nl1 >= t.n) return r;
-    const uint32_t nl2 = li + 2u < npos ? t.tbase + pos[li + 2u] : f2_next_nl(t, nl1 + 1u);
-    if (nl2 == F2_NONE || nl2 >= t.n) return r;
-    const uint32_t nl3 = li + 3u < npos ? t.tbase + pos[li + 3u] : f2_next_nl(t, nl2 + 1u);
-    if (nl3 == F2_NONE) return r;
-    r.complete = true;
-    r.end = nl3 < t.n ? nl3 + 1u : t.n;
-    // name = line.rstrip()[1:].split()[0]: drop the first byte whatever it is, skip blanks, take the token
-    uint32_t p = hs + 1u;
-    if (p < nl0 && f2_cand(t, p))
-        while (p < nl0 && is_ws(f2_byte(t, p))) ++p;
-    r.name_off = p < nl0 ? p : nl0;
-    r.nlen = p < nl0 ? f2_find_ws(t, p, nl0) - p : 0u;
-    r.seq_off = nl0 + 1u;
-    r.qual_off = nl2 + 1u;
-    r.seq_len = f2_rstrip(t, r.seq_off, nl1) - r.seq_off;
-    r.valid = r.seq_len == f2_rstrip(t, r.qual_off, nl3) - r.qual_off;
-    return r;
-}
 
 // newline flags of one word: 0x80 in every byte equal to '\n' (exact for all byte values)
 __device__ __forceinline__ uint32_t f2_nl_flags(uint32_t w)
@@ -172,21 +94,6 @@ __device__ __forceinline__ uint32_t f2_gather16(uint32_t f0, uint32_t f1, uint32
     const uint32_t hi = __dp4a(f3, 0x80402010u, __dp4a(f2, 0x08040201u, 0u));
     return (lo >> 7) | (hi << 1);
 }
-// newline / candidate masks of the 64 bytes at shared address a (16-byte aligned); the four vectors are read in
-// a rotated order so that the 8 lanes of a quarter warp hit 8 different bank groups
-__device__ __forceinline__ void f2_mask64(uint32_t a, int lane, u64 &nl, u64 &cd)
-{
-    const uint32_t rot = ((uint32_t)lane >> 1) & 3u;
-    nl = cd = 0;
-#pragma unroll
-    for (uint32_t i = 0; i < 4; ++i) {
-        const uint32_t v = (i + rot) & 3u;
-        const uint4 q = lds128(a + 16u * v);
-        nl |= (u64)f2_gather16(f2_nl_flags(q.x), f2_nl_flags(q.y), f2_nl_flags(q.z), f2_nl_flags(q.w)) << (16u * v);
-        cd |= (u64)f2_gather16(f2_c_flags(q.x), f2_c_flags(q.y), f2_c_flags(q.z), f2_c_flags(q.w)) << (16u * v);
-    }
-}
-
 // python slice [sp0:sp1] of a string of length L -> offset and length (FastqSeq.py:91-93)
 __device__ __forceinline__ void f2_clamp(const int sp[2], uint32_t L, uint32_t *a, uint32_t *n)
 {
@@ -195,247 +102,6 @@ __device__ __forceinline__ void f2_clamp(const int sp[2], uint32_t L, uint32_t *
     e = e < L ? e : L;
     *a = s;
     *n = e > s ? e - s : 0u;
-}
-
-// index read: digest of the sample-index span + raw bytes of both spans for the name suffix
-__device__ __forceinline__ void f2_digest(const BatchDev &b, const StreamDev &st, int s, const F2Tile &t, const F2Rec &r,
-                                          uint32_t v)
-{
-    uint32_t ia, in, ma, mn;
-    f2_clamp(b.span[s - 2], r.seq_len, &ia, &in);          // QUADE_SPAN_IDX1 / IDX2
-    f2_clamp(b.span[s], r.seq_len, &ma, &mn);              // QUADE_SPAN_MOL1 / MOL2
-    u64 key = 0;
-    uint32_t nm = 0, bad = in > 32u ? 1u : 0u, minq = 255u;
-    uint8_t *slot = st.sfx + (size_t)v * st.sfx_slot;
-    uint32_t word = 0;
-    for (uint32_t i = 0; i < in; ++i) {
-        uint32_t c = f2_byte(t, r.seq_off + ia + i);
-        const uint32_t q = f2_byte(t, r.qual_off + ia + i);
-        minq = q < minq ? q : minq;                         // phred = q - 33 (FastqSeq.py:44), compared later
-        word |= c << ((i & 3u) * 8u);
-        if ((i & 3u) == 3u || i + 1u == in) {
-            *reinterpret_cast<uint32_t *>(slot + (i & ~3u)) = word;
-            word = 0;
-        }
-        if (c - 'a' < 26u) c -= 32u;                        // index.seq.upper() (Sample.py:65)
-        const bool acgt = c == 'A' || c == 'C' || c == 'G' || c == 'T';
-        if (!acgt && c != 'N') bad = 1u;
-        if (i < 32u) {
-            if (acgt) key |= (u64)((c >> 1) & 3u) << (2u * i);
-            else if (c == 'N') nm |= 1u << i;
-        }
-    }
-    uint8_t *mslot = slot + ((st.wi + 3u) & ~3u);
-    for (uint32_t i = 0; i < mn; ++i) {
-        word |= f2_byte(t, r.seq_off + ma + i) << ((i & 3u) * 8u);
-        if ((i & 3u) == 3u || i + 1u == mn) {
-            *reinterpret_cast<uint32_t *>(mslot + (i & ~3u)) = word;
-            word = 0;
-        }
-    }
-    st.dig[v] = make_uint4((uint32_t)key, (uint32_t)(key >> 32), nm, in | mn << 8 | minq << 16 | bad << 24);
-}
-
-__global__ void __launch_bounds__(F2T, 6) k_frame2(const __grid_constant__ BatchDev b, uint32_t total_tiles)
-{
-    extern __shared__ __align__(128) uint8_t f2_smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t sm0 = smem_u32(f2_smem);
-    u64 *s_bm = reinterpret_cast<u64 *>(f2_smem + F2_OFF_BM);
-    u64 *s_bc = reinterpret_cast<u64 *>(f2_smem + F2_OFF_BC);
-    uint16_t *s_pos = reinterpret_cast<uint16_t *>(f2_smem + F2_OFF_POS);
-    uint32_t *s_misc = reinterpret_cast<uint32_t *>(f2_smem + F2_OFF_MISC);   // [0..8] scan, [9] base, [10..11] tickets
-    const uint32_t s_bar = sm0 + F2_OFF_MISC + 64;                            // 2 mbarriers
-    BatchState *S = b.state;
-
-    auto tile_geom = [&](uint32_t tile, int &s, uint32_t &lt) {
-        s = 0;
-        while (s + 1 < b.n_streams && tile >= b.frame_tile_start[s + 1]) ++s;
-        lt = tile - b.frame_tile_start[s];
-    };
-    auto issue = [&](uint32_t tile, uint32_t stage) {       // thread 0: TMA copy of the tile's window
-        int s;
-        uint32_t lt;
-        tile_geom(tile, s, lt);
-        const uint32_t tbase = lt * (uint32_t)F2_TILE, n16 = (b.st[s].n + 15u) & ~15u;
-        const uint32_t bytes = n16 > tbase ? min((uint32_t)F2_WIN, n16 - tbase) : 0u;
-        if (bytes) {
-            fence_proxy_async();
-            mbar_expect_tx(s_bar + 8u * stage, bytes);
-            bulk_g2s(sm0 + F2_OFF_DATA + stage * (F2_WIN + 16), b.st[s].data + tbase, bytes, s_bar + 8u * stage);
-        }
-    };
-
-    if (tid == 0) {
-        mbar_init(s_bar, 1);
-        mbar_init(s_bar + 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        const uint32_t t0 = atomicAdd(&S->ticket_frame, 1u);
-        s_misc[10] = t0;
-        if (t0 < total_tiles) issue(t0, 0);
-    }
-    __syncthreads();
-    uint32_t tile = s_misc[10], phase_bits = 0;
-
-    for (uint32_t it = 0; tile < total_tiles; ++it) {
-        const uint32_t stage = F2_STAGES == 2 ? (it & 1u) : 0u;
-        if (F2_STAGES == 2 && tid == 0) {                    // next ticket, its copy flies while this tile is parsed
-            const uint32_t tn = atomicAdd(&S->ticket_frame, 1u);
-            s_misc[10 + ((it + 1u) & 1u)] = tn;
-            if (tn < total_tiles) issue(tn, stage ^ 1u);
-        }
-        int s;
-        uint32_t lt;
-        tile_geom(tile, s, lt);
-        const StreamDev &st = b.st[s];
-        const uint32_t n = st.n, tbase = lt * (uint32_t)F2_TILE, n16 = (n + 15u) & ~15u;
-        const uint32_t staged = n16 > tbase ? min((uint32_t)F2_WIN, n16 - tbase) : 0u;
-        const uint32_t sdata = sm0 + F2_OFF_DATA + stage * (F2_WIN + 16);
-        if (staged) {
-            while (!mbar_try_wait(s_bar + 8u * stage, (phase_bits >> stage) & 1u)) {}
-            phase_bits ^= 1u << stage;
-        }
-        F2Tile T;
-        T.data = st.data;
-        T.sdata = sdata;
-        T.bm = s_bm;
-        T.bc = s_bc;
-        T.tbase = tbase;
-        T.cap = (uint32_t)F2_WIN;
-        T.n = n;
-        T.win = n > tbase ? min((uint32_t)F2_WIN, n - tbase) : 0u;
-        T.last = ((b.last >> s) & 1) != 0;
-
-        // 1. newline / candidate bitmaps of the window: 64 bytes per thread (+ the halo by warp 0)
-        u64 mine = 0, halo = 0;
-        for (int c = tid; c < F2_WORDS; c += F2T) {
-            const uint32_t c0 = (uint32_t)c * 64u;            // window offset of this chunk
-            u64 m = 0, cd = 0;
-            if (c0 < T.win) {
-                f2_mask64(sdata + c0, lane, m, cd);
-                if (c0 + 64u > T.win) {                       // bytes past the end of the file
-                    m &= (1ull << (T.win - c0)) - 1ull;
-                    cd &= (1ull << (T.win - c0)) - 1ull;
-                }
-            }
-            if (T.last && n > 0u && n - tbase >= c0 && n - tbase < c0 + 64u && f2_byte(T, n - 1u) != '\n')
-                m |= 1ull << (n - tbase - c0);                // the file's last line has no '\n'
-            s_bm[c] = m;
-            s_bc[c] = cd;
-            if (c < F2T) mine = m; else halo = m;
-        }
-        // 2. line index: block scan + look-back over the tiles of this file
-        uint32_t total;
-        const uint32_t excl = block_scan256((uint32_t)__popcll(mine), s_misc, &total);
-        uint32_t hexcl = 0, htotal = 0;                       // halo line ends (warp 0), listed after the tile's
-        if (warp == 0) {
-            const uint32_t hc = (uint32_t)__popcll(halo);
-            uint32_t inc = hc;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
-                if (lane >= o) inc += x;
-            }
-            hexcl = inc - hc;
-            htotal = __shfl_sync(0xffffffffu, inc, 31);
-            const uint32_t base = lookback(st.status_frame, (int)lt, total, lane);
-            if (lane == 0) {
-                s_misc[9] = base;
-                s_misc[12] = htotal;
-                if ((u64)tbase + F2_TILE > (u64)n) S->n_lines[s] = base + total;
-            }
-        }
-        // 3. dense list of the window's line ends; the byte after every line k = 3 (mod 4) starts a record
-        {
-            uint32_t i = excl;
-            u64 m = mine;
-            while (m) {
-                const uint32_t bit = (uint32_t)__ffsll((long long)m) - 1u;
-                m &= m - 1ull;
-                if (i < (uint32_t)F2_PCAP) s_pos[i] = (uint16_t)((uint32_t)tid * 64u + bit);
-                ++i;
-            }
-            if (warp == 0) {
-                i = total + hexcl;
-                m = halo;
-                while (m) {
-                    const uint32_t bit = (uint32_t)__ffsll((long long)m) - 1u;
-                    m &= m - 1ull;
-                    if (i < (uint32_t)F2_PCAP) s_pos[i] = (uint16_t)((uint32_t)(F2T + lane) * 64u + bit);
-                    ++i;
-                }
-            }
-        }
-        __syncthreads();
-        const uint32_t k0 = s_misc[9];
-        const uint32_t npos = min(total + s_misc[12], (uint32_t)F2_PCAP);
-        const uint32_t rbase = lt == 0u ? 0u : (k0 >> 2) + 1u;                // record index of slot 0
-        const uint32_t nslot = ((k0 + total) >> 2) - (k0 >> 2) + (lt == 0u ? 1u : 0u);
-        const uint32_t t0i = (3u - k0) & 3u;                  // list index of the first line k = 3 (mod 4)
-        // record of slot i: starts after list entry ti = t0i + 4 (i - first), its line ends are entries ti+1 .. ti+4
-        auto parse_slot = [&](uint32_t slot) -> F2Rec {
-            uint32_t hs, li;
-            if (lt == 0u && slot == 0u) { hs = 0u; li = 0u; }
-            else {
-                const uint32_t ti = t0i + 4u * (slot - (lt == 0u ? 1u : 0u));
-                li = ti + 1u;
-                hs = ti < npos ? tbase + s_pos[ti] + 1u : F2_NONE;
-            }
-            if (hs == F2_NONE) {                              // list overflow: find the terminator by bitmap search
-                uint32_t k = k0, ppos = tbase;                // (pathological tiles only: > F2_PCAP lines in 18 KiB)
-                const uint32_t want = (rbase + slot) * 4u - 1u;
-                uint32_t e = F2_NONE;
-                while (k <= want) {
-                    e = f2_next_nl(T, ppos);
-                    if (e == F2_NONE) break;
-                    ppos = e + 1u;
-                    ++k;
-                }
-                F2Rec z;
-                z.complete = z.valid = false;
-                z.name_off = z.nlen = z.seq_off = z.qual_off = z.seq_len = z.end = 0u;
-                if (e == F2_NONE) return z;
-                return f2_parse(T, e + 1u, s_pos, 0u, 0u);
-            }
-            return f2_parse(T, hs, s_pos, li, npos);
-        };
-        // 4. one thread per record start, outputs at the RAW record index j.  Records with len(seq) != len(qual)
-        //    are flagged (bit 31) and counted; they are rare, and only when a file has some does k_fix_compact
-        //    squeeze them out afterwards (pairing ordinal = rank among the valid records, FastqReader.py:48-50).
-        for (uint32_t slot = tid; slot < nslot; slot += F2T) {
-            const F2Rec R = parse_slot(slot);
-            if (!R.complete) continue;
-            const uint32_t j = rbase + slot;
-            if (j >= st.cap_rec) { S->err_capacity = 1u; continue; }
-            if (R.nlen == 0u) atomicMax(&S->first_blank[s], ~j);               // keeps the LOWEST blank record index
-            const uint32_t inv = R.valid ? 0u : 0x80000000u;
-            if (inv) atomicAdd(&S->n_invalid[s], 1u);
-            st.vend[j] = R.end;
-            if (s < 2) {
-                st.rec[j] = make_uint4(R.name_off, R.seq_off, R.qual_off, R.seq_len | inv);
-                st.vnlen[j] = R.nlen;
-            } else if (inv) {
-                st.dig[j] = make_uint4(0u, 0u, 0u, inv);
-            } else {
-                f2_digest(b, st, s, T, R, j);
-            }
-        }
-        if (F2_STAGES == 2) {
-            tile = s_misc[10 + ((it + 1u) & 1u)];
-            __syncthreads();                                  // bitmap, list and the stage are reused
-        } else {
-            // A ticket held while another tile is parsed would make every successor spin in its look-back for a
-            // whole tile time: take it just in time; the other CTAs of the SM cover the copy latency.
-            __syncthreads();
-            if (tid == 0) {
-                const uint32_t tn = atomicAdd(&S->ticket_frame, 1u);
-                s_misc[10] = tn;
-                if (tn < total_tiles) issue(tn, 0u);
-            }
-            __syncthreads();
-            tile = s_misc[10];
-        }
-    }
 }
 
 // ------------------------------------------------------------------------------------------------------------

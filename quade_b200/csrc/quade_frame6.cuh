@@ -27,9 +27,10 @@ constexpr int F6T = 256;
 #define F6_MINB 8        // 32 registers (a few spills in the parse path) and 64 resident warps: 0.653 -> 0.631 ms vs 6 CTAs at 40
 #endif
 // shared memory of a CTA: window | newline bitmap | line-end list | misc (no candidate bitmap: 24.4 KiB, 8 CTAs / SM)
-constexpr int F6_OFF_BM = F3_OFF_BM;
-constexpr int F6_OFF_POS = F6_OFF_BM + F2_WORDS * 8;            // u16[F3_PCAP]
-constexpr int F6_OFF_MISC = F6_OFF_POS + F3_PCAP * 2;
+constexpr int F6_PCAP = 2048;                  // listed line ends per window (else: redo pass)
+constexpr int F6_OFF_BM = F2_WIN + 16;
+constexpr int F6_OFF_POS = F6_OFF_BM + F2_WORDS * 8;            // u16[F6_PCAP]
+constexpr int F6_OFF_MISC = F6_OFF_POS + F6_PCAP * 2;
 constexpr int F6_SMEM = F6_OFF_MISC + 128;
 constexpr uint32_t F6_BLANK = 1u << 25;        // scratch digest: the header had no name token
 
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
         before = warp == 5 ? c5 : before;
         before = warp == 6 ? c6 : before;
         before = warp == 7 ? c7 : before;
-        const uint32_t npos = min(total + s_misc[8], (uint32_t)F3_PCAP);
+        const uint32_t npos = min(total + s_misc[8], (uint32_t)F6_PCAP);
         const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
         if (tid == 0) {
             // scratch room for the tile's records, in tile order of arrival: an upper bound over the four possible
@@ -309,7 +310,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
             if (!REDO) {
                 const uint32_t nres = first + ((total + 3u) >> 2);
                 uint32_t sb = atomicAdd(&S->scratch_cursor[s], nres);
-                if ((u64)sb + nres > (u64)st.cap_rec || total + s_misc[8] > (uint32_t)F3_PCAP) sb = F2_NONE;   // -> redo
+                if ((u64)sb + nres > (u64)st.cap_rec || total + s_misc[8] > (uint32_t)F6_PCAP) sb = F2_NONE;   // -> redo
                 s_misc[9] = sb;
             }
             if (!REDO) atomicAdd(&S->chunk_lines[s][lt / (uint32_t)kTileChunk], total);   // for k_tilescan
@@ -328,13 +329,13 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
                 if (lo) {
                     const uint32_t bit = (uint32_t)__ffs((int)lo) - 1u;
                     lo &= lo - 1u;
-                    if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(o0 + bit);
+                    if (i < (uint32_t)F6_PCAP) s_pos[i] = (uint16_t)(o0 + bit);
                     ++i;
                 }
                 if (hi) {
                     const uint32_t bit = (uint32_t)__ffs((int)hi) - 1u;
                     hi &= hi - 1u;
-                    if (ih < (uint32_t)F3_PCAP) s_pos[ih] = (uint16_t)(o0 + 32u + bit);
+                    if (ih < (uint32_t)F6_PCAP) s_pos[ih] = (uint16_t)(o0 + 32u + bit);
                     ++ih;
                 }
             }
@@ -344,7 +345,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
                 while (hm) {
                     const uint32_t bit = (uint32_t)__ffsll((long long)hm) - 1u;
                     hm &= hm - 1ull;
-                    if (i < (uint32_t)F3_PCAP) s_pos[i] = (uint16_t)(h0 + bit);
+                    if (i < (uint32_t)F6_PCAP) s_pos[i] = (uint16_t)(h0 + bit);
                     ++i;
                 }
             }
@@ -379,7 +380,7 @@ __global__ void __launch_bounds__(F6T, F6_MINB) k_frame6(const __grid_constant__
             R.complete = R.valid = false;
             R.name_off = R.nlen = R.seq_off = R.qual_off = R.seq_len = R.end = 0u;
             if (!REDO) return false;
-            const uint32_t want = (rbase + slot) * 4u - 1u;     // more than F3_PCAP lines in 18 KiB: bitmap search
+            const uint32_t want = (rbase + slot) * 4u - 1u;     // more than F6_PCAP lines in 18 KiB: bitmap search
             uint32_t k = k0, ppos = T.tbase, e = F2_NONE;
             while (k <= want) {
                 e = f2_next_nl(T, ppos);
