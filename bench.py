@@ -192,7 +192,7 @@ def run_ours(args, rank, world, local_rank):
     for t, b in zip(dev_in, pinned):
         t[:b.nbytes].copy_(torch.from_numpy(b.array), non_blocking=False)
     ctx = DemuxContext(synth.dual, synth.spans(), min_qual, synth.sample_keys(), device=local_rank,
-                       max_stream_bytes=max(sizes) + 4096, max_pairs=P + 1024, n_slots=args.slots)
+                       max_stream_bytes=max(sizes) + 4096, max_pairs=P + 1024, max_records=P + P // 8, n_slots=args.slots)
     stream = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
     ptrs = [t.data_ptr() for t in dev_in]
 

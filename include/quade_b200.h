@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define QUADE_ABI_VERSION 1
+#define QUADE_ABI_VERSION 2
 
 /* stream order = the order in which the reference pulls records inside one loop iteration
  * (src/Quade.py:211-214, :241-243): insert read 1, insert read 2, index read 1[, index read 2] */
@@ -58,12 +58,19 @@ typedef struct {
     int32_t write_pass;
     int32_t write_fail;
     int32_t n_samples;
-    /* capacities of one batch (0 = defaults: 256 MiB per stream, max_stream_bytes/64 pairs) */
+    /* capacities of one batch (0 = defaults: 256 MiB per stream, max_stream_bytes/64 pairs,
+     * max_stream_bytes/24 records per file).  A batch that holds more pairs than max_pairs is not an error: the
+     * pairs beyond are left unconsumed (quade_result.consumed) for the next batch.  More records in one file than
+     * max_records is QUADE_ERR_CAPACITY. */
     uint64_t max_stream_bytes;
     uint64_t max_pairs;
     int32_t n_slots;            /* batches in flight (1..8, 0 = 2): submit N+1 while batch N is collected */
-    int32_t reserved;
+    uint32_t flags;             /* QUADE_CTX_* */
+    uint64_t max_records;
 } quade_params;
+
+#define QUADE_CTX_DEVICE_ONLY 1u /* only QUADE_BATCH_DEVICE batches will be submitted: no pinned output arenas are
+                                    allocated at creation (they are, lazily, if a host batch comes after all) */
 
 #define QUADE_BATCH_LAST 1u   /* buffers end at end-of-file: a final line without '\n' still is a line and the
                                  leftovers are dropped (src/pyFastq/FastqReader.py:37,57-58) */
@@ -79,9 +86,9 @@ typedef struct {
     uint64_t ticket; /* caller's tag, returned by collect */
 } quade_batch;
 
-/* kernel stages timed per batch (ms_kernel[]).  FRAME: k_frame6 (newline scan, record framing, index digest);
- * VALIDATE: what turns its per-tile output into per-record arrays -- k_tilescan, k_densify, the redo pass for tiles
- * whose text defeated the record-start guess, and k_fix_* for files with len(seq) != len(qual) records
+/* kernel stages timed per batch (ms_kernel[]).  FRAME: k_frame (newline scan, record framing, index digest);
+ * VALIDATE: what turns its per-tile output into per-record tables -- k_tilescan, the redo pass for tiles whose text
+ * defeated the record-start guess, and k_locate_rare for files with len(seq) != len(qual) records
  * (FastqReader.py:48-50); PAIRING .. COMPACT: one kernel each (BINSCAN: two). */
 enum { QUADE_K_FRAME = 0, QUADE_K_VALIDATE, QUADE_K_PAIRING, QUADE_K_CLASSIFY, QUADE_K_BINSCAN, QUADE_K_OFFSETS,
        QUADE_K_COMPACT, QUADE_K_COUNT };
@@ -103,7 +110,7 @@ typedef struct {
     uint64_t in_bytes;         /* sum of consumed[] */
     uint64_t out_bytes;        /* bin_off[0][nbins] + bin_off[1][nbins] */
     uint64_t gpu_launches;     /* kernels launched for this batch */
-    uint64_t reframed_tiles;   /* 16 KiB tiles framed a second time: their text defeated the record-start guess */
+    uint64_t reframed_tiles;   /* tiles framed a second time: end of a buffer, or text that defeated the record-start guess */
 } quade_result;
 
 int quade_version(void);

@@ -84,6 +84,20 @@ static int next_valid(cursor *c, record *r)
     return 0;
 }
 
+/* passes the complete invalid records in front of the next valid one; stops before a valid record, before a record
+ * without a name token, and where the buffered complete records end */
+static void skip_invalid(cursor *c)
+{
+    for (;;) {
+        cursor t = *c;
+        record r;
+        int valid;
+        if (!next_record(&t, &r, &valid) || t.blank_seen || valid) return;
+        t.skipped++;
+        *c = t;
+    }
+}
+
 /* ---- sample registry: INDEX_TO_SAMPLE dict (Sample.py:37,151) as an open-addressing table ---- */
 typedef struct {
     int32_t *slot; /* sample id or -1 */
@@ -204,10 +218,26 @@ int qo_demux_batch(const qo_params *p, const uint8_t *const stream[4], const uin
     uint8_t keybuf[4096], molbuf[4096];
     for (;;) {                                         /* while True:  Quade.py:210 / :240 */
         record rec[4];
-        int got = 1;
-        for (int s = 0; s < ns && got > 0; s++) got = next_valid(&cur[s], &rec[s]);   /* Quade.py:211-214 */
+        cursor save[4];
+        memcpy(save, cur, sizeof(cur));
+        int got = 1, sfail = -1;
+        for (int s = 0; s < ns && got > 0; s++) { got = next_valid(&cur[s], &rec[s]); sfail = s; }   /* Quade.py:211-214 */
         if (got < 0) { err = QO_ERR_BLANK_HEADER; goto done; }
-        if (!got) break;                               /* StopIteration: end of chunk, Quade.py:223 */
+        if (!got) {
+            if (cur[sfail].last) break;                /* StopIteration: end of chunk, Quade.py:223 */
+            /* Batch semantics (the reference has no batches): the BUFFER of file sfail ran out before its end-of-file.
+             * The unfinished iteration is given back: the caller carries every tail into the next batch.  What stays
+             * consumed are the invalid records in front of each file's next valid record -- the reference skips them
+             * in their own file whatever the other files hold (FastqReader.py:48-50) -- so that a buffer holding
+             * nothing but such records makes progress; a blank header the reference may never reach is not passed. */
+            for (int s = 0; s < ns; s++) {
+                cur[s] = save[s];
+                skip_invalid(&cur[s]);
+                res->consumed[s] = cur[s].pos;
+                res->n_skipped[s] = cur[s].skipped;
+            }
+            break;
+        }
         for (int s = 0; s < ns; s++) { res->consumed[s] = cur[s].pos; res->n_skipped[s] = cur[s].skipped; }
         res->n_pairs++;                                /* Sample.TOTAL += 1, Sample.py:62 */
 

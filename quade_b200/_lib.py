@@ -8,8 +8,9 @@ from . import build as _build
 QUADE_OK = 0
 ERR_BLANK_HEADER, ERR_NOMEM, ERR_BAD_SAMPLE, ERR_CUDA, ERR_ARG, ERR_CAPACITY, ERR_UNSUPPORTED, ERR_STATE = range(-1, -9, -1)
 BATCH_LAST, BATCH_DEVICE = 1, 2
-# stage 1 (QUADE_K_VALIDATE in the header) = k_tilescan + k_densify + redo pass + k_fix_* of the k_frame6 pipeline
-K_NAMES = ["frame", "densify", "pairing", "classify", "binscan", "offsets", "compact"]
+CTX_DEVICE_ONLY = 1
+# stage 1 (QUADE_K_VALIDATE in the header) = k_tilescan + redo pass + k_locate_rare
+K_NAMES = ["frame", "tilescan", "pairing", "classify", "binscan", "offsets", "compact"]
 K_COUNT = len(K_NAMES)
 SYMBOLS = ["quade_version", "quade_last_error", "quade_device_count", "quade_host_alloc", "quade_host_free",
            "quade_ctx_create", "quade_ctx_destroy", "quade_ctx_set_samples", "quade_submit", "quade_collect",
@@ -21,7 +22,7 @@ class Params(C.Structure):
     _fields_ = [("dual", C.c_int32), ("span", (C.c_int32 * 2) * 4), ("min_qual", C.c_int32),
                 ("write_undetermined", C.c_int32), ("write_pass", C.c_int32), ("write_fail", C.c_int32),
                 ("n_samples", C.c_int32), ("max_stream_bytes", C.c_uint64), ("max_pairs", C.c_uint64),
-                ("n_slots", C.c_int32), ("reserved", C.c_int32)]
+                ("n_slots", C.c_int32), ("flags", C.c_uint32), ("max_records", C.c_uint64)]
 
 
 class Batch(C.Structure):

@@ -106,45 +106,33 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
 {
     const int ns = c->n_streams, nb = c->n_bins;
     const size_t cap_rec = c->cap_rec, cap_pairs = c->cap_pairs;
-    const size_t val_tiles = cap_rec / kValidateTile + 2;
+    const size_t tiles = c->cap_bytes / kFrameTile + 2;
     // sizes
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += up256(bytes); return o; };
-    size_t o_in[4], o_rec[4], o_vnlen[4], o_vrec[4], o_sv[4], o_vend[4], o_dig[4], o_sfx[4], o_rec_t[4], o_vnlen_t[4], o_vend_t[4], o_dig_t[4], o_sfx_t[4], o_tt[4];
+    size_t o_in[4], o_rec[4], o_nv[4], o_sfx[4], o_loc[4], o_vraw[4], o_tt[4];
     uint32_t sfx_slot[4] = {0, 0, 0, 0};
     const size_t o_zero = take(0);
     const size_t o_state = take(sizeof(BatchState));
     const size_t o_counters = take((size_t)nb * 8);
-    for (int s = 0; s < ns; ++s) {
-        o_sv[s] = take(val_tiles * 8);
-    }
     const size_t zero_end = off;
     for (int s = 0; s < ns; ++s) {
-        o_tt[s] = take((c->cap_bytes / kFrameTile + 2) * 16);
+        o_tt[s] = take(tiles * 32);
         o_in[s] = take(c->cap_bytes + 256);
         o_rec[s] = take(cap_rec * 16);
-        o_vnlen[s] = take(cap_rec * 4);
-        o_vrec[s] = take(cap_rec * 4);
-        o_vend[s] = take(cap_rec * 4);
-        o_vend_t[s] = take(cap_rec * 4);
-        o_rec_t[s] = o_vnlen_t[s] = o_dig_t[s] = o_sfx_t[s] = 0;
-        if (s < 2) {
-            o_rec_t[s] = take(cap_rec * 16);
-            o_vnlen_t[s] = take(cap_rec * 4);
-        }
-        o_dig[s] = o_sfx[s] = 0;
-        if (s >= 2) {   // index reads: digest + raw span bytes (k_frame2)
+        o_nv[s] = take(cap_rec * 8);
+        o_loc[s] = take(cap_rec * 4);
+        o_vraw[s] = take(cap_rec * 4);
+        o_sfx[s] = 0;
+        if (s >= 2) {   // index reads: raw span bytes for the name suffix
             const uint32_t wi = (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]);
             const uint32_t wm = (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]);
             sfx_slot[s] = (((wi + 3u) & ~3u) + ((wm + 3u) & ~3u) + 15u) & ~15u;
             if (sfx_slot[s] < 16u) sfx_slot[s] = 16u;
-            o_dig[s] = take(cap_rec * 16);
             o_sfx[s] = take(cap_rec * sfx_slot[s] + 64);
-            o_dig_t[s] = take(cap_rec * 16);
-            o_sfx_t[s] = take(cap_rec * sfx_slot[s] + 64);
         }
     }
-    const size_t redo_cap = (size_t)ns * (c->cap_bytes / kFrameTile + 2);
+    const size_t redo_cap = (size_t)ns * tiles;
     const size_t o_redo = take(redo_cap * 4);
     const size_t o_cls = take(cap_pairs * 4), o_len1 = take(cap_pairs * 4), o_len2 = take(cap_pairs * 4);
     const size_t o_out1 = take(cap_pairs * 4), o_out2 = take(cap_pairs * 4);
@@ -183,20 +171,13 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
         st.data = sl.d_in[s];
         st.cap_rec = (uint32_t)cap_rec;
         st.rec = reinterpret_cast<uint4 *>(A + o_rec[s]);
-        st.vnlen = reinterpret_cast<uint32_t *>(A + o_vnlen[s]);
-        st.vrec = reinterpret_cast<uint32_t *>(A + o_vrec[s]);
-        st.vend = reinterpret_cast<uint32_t *>(A + o_vend[s]);
-        st.dig = s >= 2 ? reinterpret_cast<uint4 *>(A + o_dig[s]) : nullptr;
+        st.nv = reinterpret_cast<uint2 *>(A + o_nv[s]);
+        st.loc = reinterpret_cast<uint32_t *>(A + o_loc[s]);
+        st.vraw = reinterpret_cast<uint32_t *>(A + o_vraw[s]);
         st.sfx = s >= 2 ? A + o_sfx[s] : nullptr;
-        st.vend_t = reinterpret_cast<uint32_t *>(A + o_vend_t[s]);
-        st.rec_t = s < 2 ? reinterpret_cast<uint4 *>(A + o_rec_t[s]) : nullptr;
-        st.vnlen_t = s < 2 ? reinterpret_cast<uint32_t *>(A + o_vnlen_t[s]) : nullptr;
-        st.dig_t = s >= 2 ? reinterpret_cast<uint4 *>(A + o_dig_t[s]) : nullptr;
-        st.sfx_t = s >= 2 ? A + o_sfx_t[s] : nullptr;
         st.sfx_slot = sfx_slot[s];
         st.wi = s >= 2 ? (uint32_t)(c->prm.span[s - 2][1] - c->prm.span[s - 2][0]) : 0u;
         st.wm = s >= 2 ? (uint32_t)(c->prm.span[s][1] - c->prm.span[s][0]) : 0u;
-        st.status_validate = reinterpret_cast<unsigned long long *>(A + o_sv[s]);
         st.tile_tab = reinterpret_cast<uint4 *>(A + o_tt[s]);
     }
     d.redo_list = reinterpret_cast<uint32_t *>(A + o_redo);
@@ -213,10 +194,12 @@ static int slot_alloc(quade_ctx *c, Slot &sl)
     d.out[0] = A + o_o1;
     d.out[1] = A + o_o2;
 
-    // pinned mirrors (the two output arenas are allocated lazily: device-mode callers never need them)
+    // pinned mirrors (the two output arenas only when asked for: device-mode callers never need them)
     CU(cudaHostAlloc((void **)&sl.h_state, sizeof(BatchState), cudaHostAllocDefault));
     CU(cudaHostAlloc((void **)&sl.h_bin_off, (size_t)2 * (nb + 1) * 8, cudaHostAllocDefault));
     CU(cudaHostAlloc((void **)&sl.h_counters, (size_t)nb * 8, cudaHostAllocDefault));
+    if (!(c->prm.flags & QUADE_CTX_DEVICE_ONLY))
+        for (int k = 0; k < 2; ++k) CU(cudaHostAlloc((void **)&sl.h_out[k], c->out_cap + 256, cudaHostAllocDefault));
     CU(cudaEventCreate(&sl.ev_h2d0));
     CU(cudaEventCreate(&sl.ev_h2d1));
     for (int i = 0; i < kEvents; ++i) CU(cudaEventCreate(&sl.ev_k[i]));
@@ -275,10 +258,12 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
     c->cap_bytes = (c->cap_bytes + 255) & ~255ull;
     c->cap_pairs = p->max_pairs ? p->max_pairs : c->cap_bytes / 64;
     if (c->cap_pairs < 32) c->cap_pairs = 32;
-    c->cap_rec = c->cap_pairs + c->cap_pairs / 8 + 1024;
+    // records per file and batch the scratch arrays hold: by default enough for 24-byte records (an index file of
+    // 4-base reads under short headers); a tile reserves one slot more than it may need
+    c->cap_rec = (p->max_records ? p->max_records : c->cap_bytes / 24) + c->cap_bytes / kFrameTile + 1024;
     c->suf_cap = (width + 3 + 15) & ~15u;   // 16-byte slots: k_compact3 stages them with 128-bit loads
     c->out_cap = c->cap_bytes + c->cap_pairs * c->suf_cap;
-    if (c->cap_bytes > kMaxStreamBytes || c->out_cap >= (1ull << 32) || c->cap_rec * 4 >= (1ull << 32)) {
+    if (c->cap_bytes > kMaxStreamBytes || c->out_cap >= (1ull << 32) || c->cap_rec >= (1ull << 31)) {
         delete c;
         return fail(QUADE_ERR_ARG, "batch capacity too large: stream bytes and output arena must stay below 4 GiB");
     }

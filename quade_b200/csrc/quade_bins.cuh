@@ -1,4 +1,4 @@
-// quade_kernels3.cuh -- K4 bin scans, K4b offsets, K5 compact and the launchers (included by quade_kernels.cu)
+// quade_bins.cuh -- k_binscan_* and k_offsets (included by quade_kernels.cu)
 #pragma once
 
 namespace quade {

@@ -1,4 +1,4 @@
-// quade_compact3.cuh -- K5 compact, TMA-staged (included by quade_kernels.cu)
+// quade_compact.cuh -- K5 compact, TMA-staged (included by quade_kernels.cu)
 //
 //   '@' name ':' index [':' molecular] '\n' seq '\n' '+' '\n' qual '\n'      (FastqWriter.py:61-69, FastqSeq.py:76-82)
 //
@@ -21,7 +21,7 @@ namespace quade {
 namespace {
 
 constexpr int C3_TP = kCompactTilePairs;                  // pairs per tile (upper bound; the batch's value is in BatchState)
-static_assert(C3_TP >= 1 && C3_TP <= 8, "k_compact3: one record lane per read of the tile, 16 record lanes");
+static_assert(C3_TP >= 1 && C3_TP <= 8, "k_compact: one record lane per read of the tile, 16 record lanes");
 constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stream per stage
 #ifndef QUADE_C3_HS
 #define QUADE_C3_HS 144         /* name + suffix up to 98 bytes always take the fast path (176: 130); longer ones the generic one */
@@ -61,8 +61,9 @@ __device__ __forceinline__ void seg_copy(uint32_t dst, uint32_t src, uint32_t n)
 // byte path straight from global memory: any record shape (the whole warp works on one record)
 __device__ __forceinline__ void emit_generic(const BatchDev &b, int k, uint32_t p, uint32_t cls, uint32_t ooff, int lane)
 {
-    const uint4 rc = b.st[k].rec[p];
-    const uint32_t nlen = b.st[k].vnlen[p], L = rc.w, suf_len = (cls >> 16) & 0xffu;
+    const uint32_t v = b.st[k].loc[p];
+    const uint4 rc = b.st[k].rec[v];
+    const uint32_t nlen = b.st[k].nv[v].x, L = rc.w, suf_len = (cls >> 16) & 0xffu;
     const uint8_t *sufp = b.suffix + (size_t)p * b.suf_cap, *data = b.st[k].data;
     uint8_t *gout = b.out[k] + (size_t)ooff;
     const uint32_t total = nlen + suf_len + 2u * L + 5u, D1 = 1u + nlen + suf_len, D2 = D1 + L + 3u;
@@ -124,7 +125,7 @@ struct TileMeta {
 constexpr int C3_WPC = QUADE_C3_WPC;
 static_assert(C3_SMEM % 16 == 0, "per-warp shared memory regions stay 16-byte aligned (bulk copies, 128-bit accesses)");
 
-__global__ void __launch_bounds__(32 * C3_WPC) k_compact3(const __grid_constant__ BatchDev b)
+__global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__ BatchDev b)
 {
     extern __shared__ __align__(128) uint8_t c3_smem_all[];
     const BatchState *St = b.state;
@@ -164,9 +165,10 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact3(const __grid_constant_
         m.nlen = m.cls = m.ooff = 0u;
         m.suf0 = m.suf1 = make_uint4(0, 0, 0, 0);
         if (rec_lane && tile < n_tiles && p < n_pairs) {
+            const uint32_t v = b.st[k].loc[p];                          // scratch position of the pair's record
             m.cls = b.cls[p];
-            m.rc = b.st[k].rec[p];
-            m.nlen = b.st[k].vnlen[p];
+            m.rc = b.st[k].rec[v];
+            m.nlen = b.st[k].nv[v].x;
             m.ooff = k ? b.out2[p] : b.out1[p];
             if (role == 0u && k == 0u) {                                // the pair's suffix, staged by this lane
                 const uint4 *sp = reinterpret_cast<const uint4 *>(b.suffix + (size_t)p * b.suf_cap);

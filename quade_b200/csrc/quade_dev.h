@@ -3,8 +3,16 @@
 // HBM layout of one batch slot (all offsets are u32: a stream batch is < 3.75 GiB)
 //   per stream s (R1, R2, I1[, I2]):
 //     data[n]                     the raw FASTQ bytes (16-byte aligned base)
-//     rec[cap_rec] (uint4)        per VALID record, compacted: {name_off, seq_off, qual_off, seq_len}
-//     vnlen[cap_rec], vrec[cap_rec] name_len and record index of the v-th valid record
+//     tile_tab[2 * tiles]         per frame tile: {line ends | k0, guess | ok, record slots, scratch base},
+//                                 {records with len(seq) != len(qual), first slot with a blank header, -, -}
+//     SCRATCH, indexed by the position v a tile reserved (tile order of arrival, records of a tile contiguous):
+//       rec[v] (uint4)            insert reads: {name_off, seq_off, qual_off, seq_len | invalid << 31}
+//                                 index reads:  {key lo, key hi, N mask, in | mn << 8 | lowq << 16 | bad << 24 | invalid << 31}
+//       nv[v] (uint2)             {name_len, position just after the record's last line}
+//       sfx[v * sfx_slot]         index reads: raw index bytes at [0, in), raw molecular bytes at [wi4, wi4 + mn)
+//     loc[j]                      scratch position of the j-th VALID record of the file = its pairing ordinal
+//                                 (FastqReader.py:48-50 skips a bad record in its own file only)
+//     vraw[j]                     raw record index of the j-th valid record (only written for files that hold invalid records)
 //   per pair p:
 //     cls[p]   bin | suffix_len << 16 | written << 31
 //     len1[p], len2[p]            output record bytes (0 when the bin's writer is off)
@@ -30,46 +38,39 @@ constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
 #endif
 constexpr int kCompactTilePairs = QUADE_C3_TP;   // k_compact3: pairs per tile (upper bound) ...
 constexpr int kCompactStageBytes = QUADE_C3_CAP; // ... and staged bytes per read stream and tile
-constexpr int kTileChunk = 1024;   // k_frame6 / k_tilescan: tiles per chunk of the tile table (16 MiB of input)
+constexpr int kTileChunk = 1024;   // k_frame / k_tilescan: tiles per chunk of the tile table
 constexpr int kMaxChunks = 256;    // >= kMaxStreamBytes / (16 KiB * kTileChunk)
 
 // device-resident scalars of one batch; copied back to the host as a whole
 struct BatchState {
     uint32_t n_lines[kMaxStreams];
     uint32_t n_valid[kMaxStreams];
-    uint32_t n_invalid[kMaxStreams];   // k_frame2: complete records with len(seq) != len(qual)
-    uint32_t first_blank[kMaxStreams]; // lowest record index with an empty name token, or 0xffffffff
+    uint32_t n_invalid[kMaxStreams];   // complete records with len(seq) != len(qual)
+    uint32_t first_blank[kMaxStreams]; // ~(lowest raw record index with an empty name token), 0 = none
     uint32_t n_pairs;
     uint32_t n_blocks;
     uint32_t consumed[kMaxStreams];
     uint32_t n_skipped[kMaxStreams];
     uint32_t err_capacity;             // some array would have overflowed
     uint32_t err_blank;                // blank header inside the parsed range
-    uint32_t ticket_frame;             // dynamic tile counters
-    uint32_t ticket_validate[kMaxStreams];
-    uint32_t compact_tp;               // pairs per k_compact3 tile, from the mean record size (k_pairing)
-    uint32_t scratch_cursor[kMaxStreams]; // k_frame6: records reserved in the per-stream scratch arrays
-    uint32_t n_redo, ticket_redo;      // k_frame6: tiles whose guessed record phase was wrong (malformed text)
-    uint32_t chunk_lines[kMaxStreams][kMaxChunks]; // k_frame6: line ends per chunk of kTileChunk tiles
+    uint32_t ticket_frame;             // dynamic tile counter of k_frame
+    uint32_t compact_tp;               // pairs per k_compact tile, from the mean record size (k_pairing)
+    uint32_t scratch_cursor[kMaxStreams]; // k_frame: records reserved in the per-stream scratch arrays
+    uint32_t n_redo, ticket_redo;      // tiles the fast pass could not frame (wrong guess, end of buffer, long records)
+    uint32_t chunk_lines[kMaxStreams][kMaxChunks]; // k_frame: line ends per chunk of kTileChunk tiles
     unsigned long long out_total[2];   // bytes of the R1 / R2 arenas
 };
 
 struct StreamDev {
     const uint8_t *data;
     uint32_t n;
-    uint32_t cap_rec;
+    uint32_t cap_rec;                    // record capacity of the scratch arrays and of loc / vraw
     uint4 *rec;
-    uint32_t *vnlen, *vrec;
-    // k_frame2 (fused frame + validate + index digest)
-    uint32_t *vend;                      // position just after the v-th valid record's last line
-    uint4 *dig;                          // index streams: {key lo, key hi, N mask, in | mn << 8 | min qual byte << 16 | bad << 24}
-    uint8_t *sfx;                        // index streams: raw index bytes at [0, in), raw molecular bytes at [wi, wi + mn)
-    uint4 *rec_t, *dig_t;                // scratch of k_fix_compact (rare path: files with invalid records)
-    uint32_t *vnlen_t, *vend_t;
-    uint8_t *sfx_t;
+    uint2 *nv;
+    uint8_t *sfx;
+    uint32_t *loc, *vraw;
     uint32_t sfx_slot, wi, wm;           // slot bytes (multiple of 16), widths of the index / molecular spans
-    unsigned long long *status_validate; // one per 1024-record tile
-    uint4 *tile_tab;                     // k_frame6: per 16 KiB tile {line ends | k0, guess | ok, records, scratch base}
+    uint4 *tile_tab;
 };
 
 struct HashTable {
@@ -104,7 +105,7 @@ struct BatchDev {
     long long *counters;       // [n_bins] pair counts of this batch
     uint8_t *out[2];
     uint32_t frame_tile_start[kMaxStreams + 1];
-    uint32_t *redo_list;       // k_frame6: stream << 28 | tile of the tiles to parse again
+    uint32_t *redo_list;       // stream << 28 | tile of the tiles to frame again
     uint32_t redo_cap;
 };
 
@@ -127,16 +128,18 @@ __host__ __device__ inline uint32_t key_slot(uint64_t h, uint32_t disp, uint32_t
 }
 
 // launchers (quade_kernels.cu).  All enqueue on `s`; sizes unknown to the host are read from BatchState.
-void launch_frame(const BatchDev &b, cudaStream_t s);      // k_frame6
-void launch_fix(const BatchDev &b, cudaStream_t s);        // k_tilescan, k_densify, k_frame6<redo>, k_fix_compact, k_fix_copyback
-void launch_pairing2(const BatchDev &b, cudaStream_t s);
-void launch_classify2(const BatchDev &b, cudaStream_t s);
+void launch_frame(const BatchDev &b, cudaStream_t s);      // k_frame<fast>
+void launch_fix(const BatchDev &b, cudaStream_t s);        // k_tilescan, k_frame<redo>, k_locate_rare
+void launch_pairing(const BatchDev &b, cudaStream_t s);
+void launch_classify(const BatchDev &b, cudaStream_t s);
 void launch_binscan(const BatchDev &b, cudaStream_t s);    // k_binscan_blocks, k_binscan_bins
 void launch_offsets(const BatchDev &b, cudaStream_t s);
-void launch_compact(const BatchDev &b, cudaStream_t s);    // k_compact3
+void launch_compact(const BatchDev &b, cudaStream_t s);
 size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
 
-constexpr int kFrameTile = 16384;   // bytes per frame tile (k_frame6)
-constexpr int kValidateTile = 1024; // records per validate tile
+#ifndef QUADE_F_TILE
+#define QUADE_F_TILE 32768
+#endif
+constexpr int kFrameTile = QUADE_F_TILE;   // bytes per frame tile (k_frame), 64 per thread
 
 } // namespace quade

@@ -52,7 +52,7 @@ class DemuxResult:
 
 class DemuxContext:
     def __init__(self, dual, spans, min_qual, sample_keys, write_undetermined=True, write_pass=True, write_fail=True,
-                 device=0, max_stream_bytes=0, max_pairs=0, n_slots=0):
+                 device=0, max_stream_bytes=0, max_pairs=0, n_slots=0, max_records=0, device_only=False):
         """spans: python slices (start, end) of idx1, idx2, mol1, mol2 (disabled = (0, 0)); sample_keys: fused
         index strings exactly as in the config (index1_seq + index2_seq)."""
         self._L = _lib.lib()
@@ -66,6 +66,8 @@ class DemuxContext:
         keys = [k.encode("latin-1") if isinstance(k, str) else bytes(k) for k in sample_keys]
         p.n_samples = len(keys)
         p.max_stream_bytes, p.max_pairs, p.n_slots = int(max_stream_bytes), int(max_pairs), int(n_slots)
+        p.max_records = int(max_records)
+        p.flags = _lib.CTX_DEVICE_ONLY if device_only else 0
         self.n_streams = 4 if dual else 3
         self.nbins = 1 + 2 * len(keys)
         self.n_slots = int(n_slots) or 2

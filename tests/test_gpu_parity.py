@@ -143,9 +143,8 @@ def test_error_codes_of_the_c_abi():
     with pytest.raises(QuadeError) as e:
         ctx.run([good * 300, good, good])                       # 4500 bytes > max_stream_bytes
     assert e.value.code == -6
-    with pytest.raises(QuadeError) as e:
-        ctx.run([good * 200, good * 200, good * 200])           # 200 pairs > max_pairs
-    assert e.value.code == -6
+    r = ctx.run([good * 200, good * 200, good * 200], last=False)   # 200 pairs > max_pairs: the rest is carried over
+    assert r.n_pairs == 32 and r.consumed[:3] == [32 * len(good)] * 3
     ctx.submit([good, good, good])
     with pytest.raises(QuadeError) as e:
         ctx.submit([good, good, good])                          # the only slot is in flight
@@ -279,7 +278,8 @@ def test_full_size_batch_matches_oracle_and_is_split_invariant(name):
     ctx, _ = _ctx_for(p, max_stream_bytes=max(sizes) + 4096, max_pairs=n + 1024, n_slots=1)
     r = ctx.run(streams, last=True)
     _assert_same(r, ref, p.nbins, "2 M pairs")
-    assert r.n_pairs == n and int(r.counters.sum()) == n and r.reframed_tiles == 0
+    assert r.n_pairs == n and int(r.counters.sum()) == n
+    assert r.reframed_tiles <= 2 * ns, "only the tiles at the end of each buffer take the generic pass on well-formed input"
     one_shot = [[hashlib.blake2b(r.bin_bytes(k, b), digest_size=16).digest() for b in range(p.nbins)] for k in range(2)]
     counters = r.counters.copy()
     # three ragged batches: cut points are arbitrary byte positions, different in every file
