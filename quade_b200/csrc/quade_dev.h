@@ -38,8 +38,8 @@ constexpr uint64_t kMaxStreamBytes = 0xF0000000ull;
 #endif
 constexpr int kCompactTilePairs = QUADE_C3_TP;   // k_compact3: pairs per tile (upper bound) ...
 constexpr int kCompactStageBytes = QUADE_C3_CAP; // ... and staged bytes per read stream and tile
-constexpr int kTileChunk = 1024;   // k_frame / k_tilescan: tiles per chunk of the tile table
-constexpr int kMaxChunks = 256;    // >= kMaxStreamBytes / (16 KiB * kTileChunk)
+constexpr int kTileChunk = 256;    // k_frame / k_tilescan: tiles per chunk of the tile table
+constexpr int kMaxChunks = 1024;   // >= kMaxStreamBytes / (16 KiB * kTileChunk)
 
 // device-resident scalars of one batch; copied back to the host as a whole
 struct BatchState {
@@ -57,8 +57,8 @@ struct BatchState {
     uint32_t compact_tp;               // pairs per k_compact tile, from the mean record size (k_pairing)
     uint32_t scratch_cursor[kMaxStreams]; // k_frame: records reserved in the per-stream scratch arrays
     uint32_t n_redo, ticket_redo;      // tiles the fast pass could not frame (wrong guess, end of buffer, long records)
-    uint32_t chunk_lines[kMaxStreams][kMaxChunks]; // k_frame: line ends per chunk of kTileChunk tiles
     unsigned long long out_total[2];   // bytes of the R1 / R2 arenas
+    uint32_t chunk_lines[kMaxStreams][kMaxChunks]; // k_frame: line ends per chunk of kTileChunk tiles (not copied to the host)
 };
 
 struct StreamDev {

@@ -235,8 +235,12 @@ __device__ __forceinline__ void f_token(uint32_t sm0, uint32_t hs, uint32_t nl0,
     for (;;) {
         if (m) {
             e = off + (uint32_t)__ffsll((long long)m) - 1u;
+            if (e >= nl0) { e = nl0; break; }                  // nl0 may be the virtual end of a buffer without a final '\n'
             if (is_ws(lds8(sm0 + e))) break;
             m &= m - 1ull;                                     // a control character inside the token
+        } else if (off + 64u > nl0) {
+            e = nl0;
+            break;
         } else {
             off += 64u;
             m = f_cand64(sm0 + off);
@@ -473,7 +477,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         const uint32_t npos = REDO ? min(total + halo_all, (uint32_t)FT_PCAP) : total + min(halo_all, 4u);
         const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
         const uint32_t nres = first + ((total + 3u) >> 2);      // upper bound of the tile's record slots over the 4 phases
-        const bool listed = REDO || (!edge && npos <= (uint32_t)FT_PCAP);
+        const bool listed = REDO || npos <= (uint32_t)FT_PCAP;
         uint32_t sb_reg = 0u, tk_reg = 0u;
         if (tid == 0) {
             // scratch room for the tile's records, in tile order of arrival, and the next ticket: both atomics fly
@@ -604,8 +608,10 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                 hs = lds16(a_pos + 2u * ti) + 1u;
                 li = ti + 1u;
             }
-            if (li + 4u > npos) {                               // the record does not end inside the window: redo
-                s_misc[FM_BAD] = 1u;
+            if (li + 4u > npos) {
+                // the record does not end inside the window: the trailing partial record of the buffer
+                // (FastqReader.py:57-58; the caller carries it over), or a record for the redo pass
+                if (!edge) s_misc[FM_BAD] = 1u;
                 return false;
             }
             const uint32_t nl0 = lds16(a_pos + 2u * li), nl1 = lds16(a_pos + 2u * li + 2u), nl2 = lds16(a_pos + 2u * li + 4u),
@@ -615,7 +621,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             const uint32_t sq = nl0 + 1u, qq = nl2 + 1u;
             const uint32_t L = f_rstrip(sm0, sq, nl1) - sq;
             const bool valid = L == f_rstrip(sm0, qq, nl3) - qq;
-            o_nv = make_uint2(nlen, tbase + nl3 + 1u);
+            o_nv = make_uint2(nlen, min(tbase + nl3 + 1u, n));   // a virtual last line end sits AT n
             if (nlen == 0u) atomicMin(&s_misc[FM_BLANK], slot);
             if (!valid) atomicAdd(&s_misc[FM_NINV], 1u);
             if (s < 2) {
@@ -678,8 +684,12 @@ __global__ void __launch_bounds__(kTileChunk) k_tilescan(const __grid_constant__
     if (tid == 0) s_base = s_all = 0u;
     __syncthreads();
     {                                                           // line ends in the chunks before this one, and in all
-        const uint32_t c = tid < kMaxChunks ? S->chunk_lines[s][tid] : 0u;
-        uint32_t v = (uint32_t)tid < chunk ? c : 0u, a = c;
+        uint32_t v = 0u, a = 0u;
+        for (uint32_t c = (uint32_t)tid; c < (uint32_t)kMaxChunks; c += (uint32_t)kTileChunk) {
+            const uint32_t x = S->chunk_lines[s][c];
+            a += x;
+            v += c < chunk ? x : 0u;
+        }
 #pragma unroll
         for (int o = 16; o; o >>= 1) {
             v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -700,7 +710,7 @@ __global__ void __launch_bounds__(kTileChunk) k_tilescan(const __grid_constant__
     if (lane == 31) s_warp[warp] = inc;
     __syncthreads();
     if (warp == 0) {
-        const uint32_t w = s_warp[lane];
+        const uint32_t w = lane < kTileChunk / 32 ? s_warp[lane] : 0u;
         uint32_t wi = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -778,7 +788,7 @@ __global__ void __launch_bounds__(kTileChunk) k_locate_rare(const __grid_constan
         if (lane == 31) s_warp[warp] = inc;
         __syncthreads();
         if (warp == 0) {
-            const uint32_t w = s_warp[lane];
+            const uint32_t w = lane < kTileChunk / 32 ? s_warp[lane] : 0u;
             uint32_t wi = w;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
