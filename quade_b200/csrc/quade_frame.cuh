@@ -36,6 +36,18 @@ constexpr int FT_PCAP = FT_TILE * 3 / 16;      // listed line ends per window: r
 constexpr uint32_t FT_NONE = 0xffffffffu;
 static_assert(FT_HALO / 64 == 32, "the halo's bitmap words are scanned by one warp");
 static_assert(FT_NW >= 2 && FT_NW <= 32 && FT_WIN < 65536, "line ends are listed as u16 window offsets");
+#ifndef QUADE_F_REGBM
+#define QUADE_F_REGBM 1                        // fast pass: bitmap words stay in registers, incremental halo scan
+#endif
+#ifndef QUADE_F_POLL1
+#define QUADE_F_POLL1 0                        // one lane per warp spins on the copy's mbarrier: measured slower (0.504 vs 0.477 ms)
+#endif
+#ifndef QUADE_F_GUESSW
+#define QUADE_F_GUESSW 0                       // only the warps that can own a record slot guess the record phase: measured slower (0.476 vs 0.456 ms)
+#endif
+#ifndef QUADE_F_IDXTOK
+#define QUADE_F_IDXTOK 0                       // index reads: full name token scan (only "is there a token" is needed)
+#endif
 #ifndef QUADE_F_MINB
 #define QUADE_F_MINB (2048 / FT_NT)            // 64 resident warps at 32 registers
 #endif
@@ -403,27 +415,57 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         const bool lastbuf = ((b.last >> s) & 1) != 0;
         const bool edge = win < (uint32_t)FT_WIN;               // the window reaches the end of the buffer
         if (((n + 15u) & ~15u) > tbase) {                       // a copy was issued for this tile
-            while (!mbar_try_wait(s_bar, phase)) {}
+            if (QUADE_F_POLL1) {
+                if (lane == 0)
+                    while (!mbar_try_wait(s_bar, phase)) {}     // one lane spins ...
+                __syncwarp();
+            }
+            while (!mbar_try_wait(s_bar, phase)) {}             // ... every thread observes the completed phase once
             phase ^= 1u;
         }
 
-        // 1. newline masks: thread t takes the 16-byte chunks t, t + FT_NT, ... (conflict-free 128-bit loads); the
-        //    16-bit masks stored per chunk ARE the 64-bit bitmap words
-        if (!edge) {                                            // the usual tile: nothing to clip
+        // 1. newline masks.  Fast pass: thread t owns the 64 bytes of bitmap word t; its four 16-byte vectors are read
+        //    in an order rotated by the lane so that the 8 lanes of a quarter warp hit 8 different bank groups, and the
+        //    four 16-bit masks are put in place by ONE 64-bit rotation: the word never leaves the registers.
+        //    Redo pass: thread t takes the chunks t, t + FT_NT, ... and the masks go to the shared bitmap that the
+        //    generic parser searches.
+        u64 mine;
+        constexpr bool REGBM = !REDO && QUADE_F_REGBM;
+        if (REGBM) {
+            const uint32_t rot = ((uint32_t)lane >> 1) & 3u, a = sm0 + 64u * (uint32_t)tid;
+            uint32_t r[4];
 #pragma unroll
-            for (uint32_t i = 0; i < 5; ++i) {
-                const uint32_t c = (uint32_t)tid + (uint32_t)FT_NT * i;
-                if (i == 4 && tid >= FT_HALO / 16) break;       // halo: 128 chunks
-                const uint4 q = lds128(sm0 + 16u * c);
-                sts16(sm0 + FT_OFF_BM + 2u * c, f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w)));
+            for (uint32_t i = 0; i < 4; ++i) {
+                const uint4 q = lds128(a + 16u * ((i + rot) & 3u));
+                r[i] = f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w));
+            }
+            uint32_t xl = r[0] | r[1] << 16, xh = r[2] | r[3] << 16;     // mask of vector (i + rot) & 3 at bits 16 i
+            if (rot & 2u) { const uint32_t t = xl; xl = xh; xh = t; }
+            const uint32_t sh = (rot & 1u) * 16u;                        // ... rotated left by 16 rot: vector v at bits 16 v
+            mine = (u64)__funnelshift_l(xl, xh, sh) << 32 | __funnelshift_l(xh, xl, sh);
+            if (edge) {                                         // the window reaches the end of the buffer: clip
+                const uint32_t o0 = 64u * (uint32_t)tid;
+                mine = o0 >= win ? 0ull : (win - o0 >= 64u ? mine : mine & ((1ull << (win - o0)) - 1ull));
+                if (lastbuf && n > 0u && n - tbase == o0 + ((n - tbase) & 63u) && n - tbase < (uint32_t)FT_TILE + 64u &&
+                    st.data[n - 1u] != '\n')
+                    mine |= 1ull << ((n - tbase) & 63u);         // no final '\n': a virtual line end AT n
             }
         } else {
             uint32_t vbit = FT_NONE;                            // window offset of a virtual last line end
             if (lastbuf && n > 0u && n - tbase < (uint32_t)FT_WIN) vbit = n - tbase;
+            if (!edge) {                                        // the usual tile: nothing to clip
+#pragma unroll
+                for (uint32_t i = 0; i < 5; ++i) {
+                    const uint32_t c = (uint32_t)tid + (uint32_t)FT_NT * i;
+                    if (i == 4 && tid >= FT_HALO / 16) break;   // halo: 128 chunks
+                    const uint4 q = lds128(sm0 + 16u * c);
+                    sts16(sm0 + FT_OFF_BM + 2u * c, f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w)));
+                }
+            } else
 #pragma unroll 1
             for (uint32_t i = 0; i < 5; ++i) {
                 const uint32_t c = (uint32_t)tid + (uint32_t)FT_NT * i, off = 16u * c;
-                if (i == 4 && tid >= FT_HALO / 16) break;
+                if (i == 4 && tid >= FT_HALO / 16) break;       // halo: 128 chunks
                 uint32_t m = 0u;
                 if (off < win) {
                     const uint4 q = lds128(sm0 + off);
@@ -433,11 +475,11 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                 if ((vbit >> 4) == c && st.data[n - 1u] != '\n') m |= 1u << (vbit & 15u);   // no final '\n'
                 sts16(sm0 + FT_OFF_BM + 2u * c, m);
             }
+            __syncthreads();                                    // bitmap complete
+            mine = s_bm[tid];
         }
-        __syncthreads();                                        // B1: bitmap complete
 
-        // 2. line ends per thread (64 bytes = bitmap word tid), warp scans; the halo's 32 words by warp 1
-        const u64 mine = s_bm[tid];
+        // 2. line ends per thread, warp scans (redo pass: the halo's 32 words by warp 1)
         const uint32_t cnt = (uint32_t)__popcll(mine);
         uint32_t inc = cnt;
 #pragma unroll
@@ -448,7 +490,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         if (lane == 31) s_misc[warp] = inc;
         u64 hm = 0;
         uint32_t hinc = 0, hcnt = 0;
-        if (warp == 1) {
+        if (!REGBM && warp == 1) {
             hm = s_bm[FT_NT + lane];
             hcnt = (uint32_t)__popcll(hm);
             hinc = hcnt;
@@ -472,12 +514,11 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             before = __shfl_sync(0xffffffffu, wi - w, warp);
             total = __shfl_sync(0xffffffffu, wi, FT_NW - 1);
         }
-        const uint32_t halo_all = s_misc[FM_HALO];
         // the fast pass needs the halo only for the record that starts last in the tile: 4 line ends at most
-        const uint32_t npos = REDO ? min(total + halo_all, (uint32_t)FT_PCAP) : total + min(halo_all, 4u);
+        uint32_t npos = REDO ? min(total + s_misc[FM_HALO], (uint32_t)FT_PCAP) : total + min(s_misc[FM_HALO], 4u);
         const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
         const uint32_t nres = first + ((total + 3u) >> 2);      // upper bound of the tile's record slots over the 4 phases
-        const bool listed = REDO || npos <= (uint32_t)FT_PCAP;
+        const bool listed = REDO || total + 4u <= (uint32_t)FT_PCAP;
         uint32_t sb_reg = 0u, tk_reg = 0u;
         if (tid == 0) {
             // scratch room for the tile's records, in tile order of arrival, and the next ticket: both atomics fly
@@ -508,7 +549,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                     ++ih;
                 }
             }
-            if (warp == 1) {
+            if (!REGBM && warp == 1) {
                 i = total + hinc - hcnt;
                 const uint32_t h0 = (uint32_t)(FT_NT + lane) * 64u;
                 while (hm && i < npos) {
@@ -518,19 +559,50 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                     ++i;
                 }
             }
+            if (REGBM && warp == 1) {
+                // the first 4 line ends of the halo, 512 bytes (one vector per lane) at a time: 2 x 150 reads need one step
+                uint32_t found = 0u;
+                for (uint32_t h = 0; h < (uint32_t)FT_HALO / 512u && found < 4u; ++h) {
+                    const uint32_t off = (uint32_t)FT_TILE + 512u * h + 16u * (uint32_t)lane;
+                    uint32_t m = 0u;
+                    if (off < win) {
+                        const uint4 q = lds128(sm0 + off);
+                        m = f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w));
+                        if (win - off < 16u) m &= (1u << (win - off)) - 1u;
+                    }
+                    if (edge && lastbuf && n > 0u && ((n - tbase) >> 4) == (off >> 4) && st.data[n - 1u] != '\n')
+                        m |= 1u << ((n - tbase) & 15u);
+                    const uint32_t c = (uint32_t)__popc(m);
+                    uint32_t ci = c;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t x = __shfl_up_sync(0xffffffffu, ci, o);
+                        if (lane >= o) ci += x;
+                    }
+                    uint32_t r = found + ci - c;
+                    while (m && r < 4u) {
+                        s_pos[total + r] = (uint16_t)(off + (uint32_t)__ffs((int)m) - 1u);
+                        m &= m - 1u;
+                        ++r;
+                    }
+                    found += __shfl_sync(0xffffffffu, ci, 31);
+                }
+                if (lane == 0) s_misc[FM_HALO] = min(found, 4u);
+            }
         }
         if (tid == 0) {
             ticket_put(half ^ 1u, tk_reg);
             if (!REDO) s_misc[FM_BASE] = (u64)sb_reg + nres > (u64)st.cap_rec ? FT_NONE : sb_reg;
         }
         __syncthreads();                                        // B3: list complete, next ticket and scratch base known
+        if (REGBM) npos = total + s_misc[FM_HALO];
 
         // 4. which list entries close a record: the true k0 (redo) or the guess from the text
         uint32_t t0 = 3u, k0 = 0u;                              // t0: list index of the first record-closing line end
         if (REDO) {
             k0 = st.tile_tab[2u * lt].x;
             t0 = (3u - k0) & 3u;
-        } else if (lt != 0u && listed) {
+        } else if (lt != 0u && listed && (!QUADE_F_GUESSW || (uint32_t)warp * 32u < nres)) {   // warps that can own a record slot
             bool ok = false;
             if (lane < 4 && (uint32_t)lane + 2u < npos)
                 ok = lds8(sm0 + lds16(a_pos + 2u * lane) + 1u) == '@' && lds8(sm0 + lds16(a_pos + 2u * (lane + 2)) + 1u) == '+';
@@ -617,7 +689,12 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             const uint32_t nl0 = lds16(a_pos + 2u * li), nl1 = lds16(a_pos + 2u * li + 2u), nl2 = lds16(a_pos + 2u * li + 4u),
                            nl3 = lds16(a_pos + 2u * li + 6u);
             uint32_t noff, nlen;
-            f_token(sm0, hs, nl0, noff, nlen);
+            if (s < 2 || QUADE_F_IDXTOK) f_token(sm0, hs, nl0, noff, nlen);
+            else {                                              // index reads: only whether there is a name token matters
+                noff = hs + 1u;
+                while (noff < nl0 && is_ws(lds8(sm0 + noff))) ++noff;
+                nlen = noff < nl0 ? 1u : 0u;
+            }
             const uint32_t sq = nl0 + 1u, qq = nl2 + 1u;
             const uint32_t L = f_rstrip(sm0, sq, nl1) - sq;
             const bool valid = L == f_rstrip(sm0, qq, nl3) - qq;

@@ -1,9 +1,16 @@
 #!/bin/bash
-# A/B of kernel variants on the GPU box: parity tests + per-kernel timings under each environment setting.
-# usage (under gpurun): bash tools/gpu_ab.sh "QUADE_FRAME=3" ["QUADE_FRAME=2" ...]
+# A/B/C... of library builds on one box: A = in-tree libquade_b200.so, the others = quade_b200/libquade_b200_<sfx>.so
+# (tools/build_variant.sh).  Kernel-only bench lines alternate over two rounds; the parity tests run on every variant.
+# usage (under gpurun): bash tools/gpu_ab.sh tag sfx1 [sfx2 ...]
+tag=$1; shift
 mkdir -p gpurun_out
-for envs in "$@"; do
-  echo "=== $envs"
-  env $envs timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-  env $envs timeout 300 python tools/probe_steps.py 2>&1 | tail -2
+for r in 1 2; do for v in A "$@"; do
+  if [ $v = A ]; then unset QUADE_LIB_PATH; else export QUADE_LIB_PATH=$PWD/quade_b200/libquade_b200_$v.so; fi
+  python bench.py --steps 40 --warmup 3 --no-e2e --no-cpu-baseline 2>/dev/null | python -c "
+import sys, json
+d = json.loads(sys.stdin.readline())
+print('$v', round(d['ms_per_step'], 4), {k: round(x['ms'], 4) for k, x in d['roofline']['per_kernel'].items()})"
+done; done | tee gpurun_out/${tag}_ab.txt
+for v in "$@"; do
+  QUADE_LIB_PATH=$PWD/quade_b200/libquade_b200_$v.so timeout 300 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -2 | sed "s/^/$v: /" | tee -a gpurun_out/${tag}_ab.txt
 done
