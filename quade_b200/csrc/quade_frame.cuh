@@ -27,7 +27,11 @@ namespace quade {
 namespace {
 
 constexpr int FT_TILE = kFrameTile;            // bytes owned by a tile
-constexpr int FT_NT = FT_TILE / 64;            // threads per CTA: one 64-byte bitmap word each
+#ifndef QUADE_F_WPT
+#define QUADE_F_WPT 2
+#endif
+constexpr int FT_WPT = QUADE_F_WPT;            // 64-byte bitmap words per thread
+constexpr int FT_NT = FT_TILE / 64 / FT_WPT;   // threads per CTA
 constexpr int FT_NW = FT_NT / 32;
 constexpr int FT_HALO = 2048;                  // bytes after the tile that are staged as well
 constexpr int FT_WIN = FT_TILE + FT_HALO;
@@ -36,9 +40,7 @@ constexpr int FT_PCAP = FT_TILE * 3 / 16;      // listed line ends per window: r
 constexpr uint32_t FT_NONE = 0xffffffffu;
 static_assert(FT_HALO / 64 == 32, "the halo's bitmap words are scanned by one warp");
 static_assert(FT_NW >= 2 && FT_NW <= 32 && FT_WIN < 65536, "line ends are listed as u16 window offsets");
-#ifndef QUADE_F_REGBM
-#define QUADE_F_REGBM 1                        // fast pass: bitmap words stay in registers, incremental halo scan
-#endif
+static_assert(FT_WPT == 1 || FT_WPT == 2, "the line-end counts of a thread's words share one register in the scans");
 #ifndef QUADE_F_POLL1
 #define QUADE_F_POLL1 0                        // one lane per warp spins on the copy's mbarrier: measured slower (0.504 vs 0.477 ms)
 #endif
@@ -49,7 +51,7 @@ static_assert(FT_NW >= 2 && FT_NW <= 32 && FT_WIN < 65536, "line ends are listed
 #define QUADE_F_IDXTOK 0                       // index reads: full name token scan (only "is there a token" is needed)
 #endif
 #ifndef QUADE_F_MINB
-#define QUADE_F_MINB (2048 / FT_NT)            // 64 resident warps at 32 registers
+#define QUADE_F_MINB 4                         // as many CTAs as the shared memory of an SM holds (32 KiB tiles)
 #endif
 
 // shared memory of a CTA: window (+ slack for the 64-byte header scan) | newline bitmap | line-end list | misc
@@ -424,48 +426,38 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             phase ^= 1u;
         }
 
-        // 1. newline masks.  Fast pass: thread t owns the 64 bytes of bitmap word t; its four 16-byte vectors are read
-        //    in an order rotated by the lane so that the 8 lanes of a quarter warp hit 8 different bank groups, and the
-        //    four 16-bit masks are put in place by ONE 64-bit rotation: the word never leaves the registers.
-        //    Redo pass: thread t takes the chunks t, t + FT_NT, ... and the masks go to the shared bitmap that the
-        //    generic parser searches.
-        u64 mine;
-        constexpr bool REGBM = !REDO && QUADE_F_REGBM;
-        if (REGBM) {
-            const uint32_t rot = ((uint32_t)lane >> 1) & 3u, a = sm0 + 64u * (uint32_t)tid;
-            uint32_t r[4];
+        // 1. newline masks.  Fast pass: thread t owns the 64 bytes of the bitmap words t, t + FT_NT, ...; the four
+        //    16-byte vectors of a word are read in an order rotated by the lane so that the 8 lanes of a quarter warp
+        //    hit 8 different bank groups, and the four 16-bit masks are put in place by ONE 64-bit rotation: the words
+        //    never leave the registers.  Redo pass: the masks go to the shared bitmap that the generic parser searches.
+        u64 mine[FT_WPT];
+        if (!REDO) {
+            const uint32_t rot = ((uint32_t)lane >> 1) & 3u, sh = (rot & 1u) * 16u;
 #pragma unroll
-            for (uint32_t i = 0; i < 4; ++i) {
-                const uint4 q = lds128(a + 16u * ((i + rot) & 3u));
-                r[i] = f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w));
-            }
-            uint32_t xl = r[0] | r[1] << 16, xh = r[2] | r[3] << 16;     // mask of vector (i + rot) & 3 at bits 16 i
-            if (rot & 2u) { const uint32_t t = xl; xl = xh; xh = t; }
-            const uint32_t sh = (rot & 1u) * 16u;                        // ... rotated left by 16 rot: vector v at bits 16 v
-            mine = (u64)__funnelshift_l(xl, xh, sh) << 32 | __funnelshift_l(xh, xl, sh);
-            if (edge) {                                         // the window reaches the end of the buffer: clip
-                const uint32_t o0 = 64u * (uint32_t)tid;
-                mine = o0 >= win ? 0ull : (win - o0 >= 64u ? mine : mine & ((1ull << (win - o0)) - 1ull));
-                if (lastbuf && n > 0u && n - tbase == o0 + ((n - tbase) & 63u) && n - tbase < (uint32_t)FT_TILE + 64u &&
-                    st.data[n - 1u] != '\n')
-                    mine |= 1ull << ((n - tbase) & 63u);         // no final '\n': a virtual line end AT n
+            for (int w = 0; w < FT_WPT; ++w) {
+                const uint32_t o0 = 64u * ((uint32_t)tid + (uint32_t)(w * FT_NT)), a = sm0 + o0;
+                uint32_t r[4];
+#pragma unroll
+                for (uint32_t i = 0; i < 4; ++i) {
+                    const uint4 q = lds128(a + 16u * ((i + rot) & 3u));
+                    r[i] = f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w));
+                }
+                uint32_t xl = r[0] | r[1] << 16, xh = r[2] | r[3] << 16;   // mask of vector (i + rot) & 3 at bits 16 i
+                if (rot & 2u) { const uint32_t t = xl; xl = xh; xh = t; }  // ... rotated left by 16 rot: vector v at bits 16 v
+                u64 m = (u64)__funnelshift_l(xl, xh, sh) << 32 | __funnelshift_l(xh, xl, sh);
+                if (edge) {                                     // the window reaches the end of the buffer: clip
+                    m = o0 >= win ? 0ull : (win - o0 >= 64u ? m : m & ((1ull << (win - o0)) - 1ull));
+                    if (lastbuf && n > 0u && ((n - tbase) >> 6) == (o0 >> 6) && st.data[n - 1u] != '\n')
+                        m |= 1ull << ((n - tbase) & 63u);        // no final '\n': a virtual line end AT n
+                }
+                mine[w] = m;
             }
         } else {
             uint32_t vbit = FT_NONE;                            // window offset of a virtual last line end
             if (lastbuf && n > 0u && n - tbase < (uint32_t)FT_WIN) vbit = n - tbase;
-            if (!edge) {                                        // the usual tile: nothing to clip
-#pragma unroll
-                for (uint32_t i = 0; i < 5; ++i) {
-                    const uint32_t c = (uint32_t)tid + (uint32_t)FT_NT * i;
-                    if (i == 4 && tid >= FT_HALO / 16) break;   // halo: 128 chunks
-                    const uint4 q = lds128(sm0 + 16u * c);
-                    sts16(sm0 + FT_OFF_BM + 2u * c, f_gather16(f_nl_flags(q.x), f_nl_flags(q.y), f_nl_flags(q.z), f_nl_flags(q.w)));
-                }
-            } else
 #pragma unroll 1
-            for (uint32_t i = 0; i < 5; ++i) {
-                const uint32_t c = (uint32_t)tid + (uint32_t)FT_NT * i, off = 16u * c;
-                if (i == 4 && tid >= FT_HALO / 16) break;       // halo: 128 chunks
+            for (uint32_t c = (uint32_t)tid; c < (uint32_t)FT_WIN / 16u; c += (uint32_t)FT_NT) {
+                const uint32_t off = 16u * c;
                 uint32_t m = 0u;
                 if (off < win) {
                     const uint4 q = lds128(sm0 + off);
@@ -476,11 +468,15 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                 sts16(sm0 + FT_OFF_BM + 2u * c, m);
             }
             __syncthreads();                                    // bitmap complete
-            mine = s_bm[tid];
+#pragma unroll
+            for (int w = 0; w < FT_WPT; ++w) mine[w] = s_bm[tid + w * FT_NT];
         }
 
-        // 2. line ends per thread, warp scans (redo pass: the halo's 32 words by warp 1)
-        const uint32_t cnt = (uint32_t)__popcll(mine);
+        // 2. line ends per thread; ONE warp scan for all words of a thread: their counts (<= 64 each, <= 2^14 per tile
+        //    and word row) travel as 16-bit fields of one register.  Redo pass: the halo's 32 words by warp 1
+        uint32_t cnt = 0u;
+#pragma unroll
+        for (int w = 0; w < FT_WPT; ++w) cnt |= (uint32_t)__popcll(mine[w]) << (16 * w);
         uint32_t inc = cnt;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -490,8 +486,8 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         if (lane == 31) s_misc[warp] = inc;
         u64 hm = 0;
         uint32_t hinc = 0, hcnt = 0;
-        if (!REGBM && warp == 1) {
-            hm = s_bm[FT_NT + lane];
+        if (REDO && warp == 1) {
+            hm = s_bm[FT_TILE / 64 + lane];
             hcnt = (uint32_t)__popcll(hm);
             hinc = hcnt;
 #pragma unroll
@@ -502,7 +498,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             if (lane == 31) s_misc[FM_HALO] = hinc;
         }
         __syncthreads();                                        // B2: warp counts
-        uint32_t before, total;
+        uint32_t before[FT_WPT], total = 0u;                    // line ends of the tile before each of the thread's words
         {                                                       // exclusive prefix over the warps, by every warp
             const uint32_t w = lane < FT_NW ? s_misc[lane] : 0u;
             uint32_t wi = w;
@@ -511,11 +507,15 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                 const uint32_t x = __shfl_up_sync(0xffffffffu, wi, o);
                 if (lane >= o) wi += x;
             }
-            before = __shfl_sync(0xffffffffu, wi - w, warp);
-            total = __shfl_sync(0xffffffffu, wi, FT_NW - 1);
+            const uint32_t bw = __shfl_sync(0xffffffffu, wi - w, warp) + inc - cnt, tw = __shfl_sync(0xffffffffu, wi, FT_NW - 1);
+#pragma unroll
+            for (int w2 = 0; w2 < FT_WPT; ++w2) {               // word row w2 lies after all of the rows before it
+                before[w2] = total + ((bw >> (16 * w2)) & 0xffffu);
+                total += (tw >> (16 * w2)) & 0xffffu;
+            }
         }
         // the fast pass needs the halo only for the record that starts last in the tile: 4 line ends at most
-        uint32_t npos = REDO ? min(total + s_misc[FM_HALO], (uint32_t)FT_PCAP) : total + min(s_misc[FM_HALO], 4u);
+        uint32_t npos = REDO ? min(total + s_misc[FM_HALO], (uint32_t)FT_PCAP) : 0u;
         const uint32_t first = lt == 0u ? 1u : 0u;              // slot 0 of a file's first tile starts at byte 0
         const uint32_t nres = first + ((total + 3u) >> 2);      // upper bound of the tile's record slots over the 4 phases
         const bool listed = REDO || total + 4u <= (uint32_t)FT_PCAP;
@@ -530,28 +530,35 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
 
         // 3. dense list of the window's line ends (tile, then halo: list order = byte order)
         if (listed) {
-            uint32_t i = before + inc - cnt;
-            uint32_t lo = (uint32_t)mine, hi = (uint32_t)(mine >> 32);
-            const uint32_t o0 = (uint32_t)tid * 64u;
-            // both halves of the word advance in the same iteration: the warp loops max(popc(lo), popc(hi)) times
-            uint32_t ih = i + (uint32_t)__popc(lo);
-            while (lo | hi) {
-                if (lo) {
-                    const uint32_t bit = (uint32_t)__ffs((int)lo) - 1u;
-                    lo &= lo - 1u;
-                    if (!REDO || i < (uint32_t)FT_PCAP) s_pos[i] = (uint16_t)(o0 + bit);
-                    ++i;
-                }
-                if (hi) {
-                    const uint32_t bit = (uint32_t)__ffs((int)hi) - 1u;
-                    hi &= hi - 1u;
-                    if (!REDO || ih < (uint32_t)FT_PCAP) s_pos[ih] = (uint16_t)(o0 + 32u + bit);
-                    ++ih;
+            // all 32-bit halves of the thread's words advance in the same iteration: the warp loops as often as its
+            // fullest half has line ends
+            uint32_t hb[2 * FT_WPT], hi_[2 * FT_WPT];          // bits left / list index, per half
+            uint32_t any = 0u;
+#pragma unroll
+            for (int w = 0; w < FT_WPT; ++w) {
+                hb[2 * w] = (uint32_t)mine[w];
+                hb[2 * w + 1] = (uint32_t)(mine[w] >> 32);
+                hi_[2 * w] = before[w];
+                hi_[2 * w + 1] = before[w] + (uint32_t)__popc(hb[2 * w]);
+                any |= hb[2 * w] | hb[2 * w + 1];
+            }
+            while (any) {
+                any = 0u;
+#pragma unroll
+                for (int h = 0; h < 2 * FT_WPT; ++h) {
+                    if (hb[h]) {
+                        const uint32_t bit = (uint32_t)__ffs((int)hb[h]) - 1u;
+                        hb[h] &= hb[h] - 1u;
+                        const uint32_t o0 = 64u * ((uint32_t)tid + (uint32_t)((h >> 1) * FT_NT)) + 32u * (uint32_t)(h & 1);
+                        if (!REDO || hi_[h] < (uint32_t)FT_PCAP) s_pos[hi_[h]] = (uint16_t)(o0 + bit);
+                        ++hi_[h];
+                        any |= hb[h];
+                    }
                 }
             }
-            if (!REGBM && warp == 1) {
-                i = total + hinc - hcnt;
-                const uint32_t h0 = (uint32_t)(FT_NT + lane) * 64u;
+            if (REDO && warp == 1) {
+                uint32_t i = total + hinc - hcnt;
+                const uint32_t h0 = (uint32_t)(FT_TILE / 64 + lane) * 64u;
                 while (hm && i < npos) {
                     const uint32_t bit = (uint32_t)__ffsll((long long)hm) - 1u;
                     hm &= hm - 1ull;
@@ -559,7 +566,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                     ++i;
                 }
             }
-            if (REGBM && warp == 1) {
+            if (!REDO && warp == 1) {
                 // the first 4 line ends of the halo, 512 bytes (one vector per lane) at a time: 2 x 150 reads need one step
                 uint32_t found = 0u;
                 for (uint32_t h = 0; h < (uint32_t)FT_HALO / 512u && found < 4u; ++h) {
@@ -595,7 +602,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             if (!REDO) s_misc[FM_BASE] = (u64)sb_reg + nres > (u64)st.cap_rec ? FT_NONE : sb_reg;
         }
         __syncthreads();                                        // B3: list complete, next ticket and scratch base known
-        if (REGBM) npos = total + s_misc[FM_HALO];
+        if (!REDO) npos = total + s_misc[FM_HALO];
 
         // 4. which list entries close a record: the true k0 (redo) or the guess from the text
         uint32_t t0 = 3u, k0 = 0u;                              // t0: list index of the first record-closing line end
