@@ -36,11 +36,16 @@ constexpr int FT_NW = FT_NT / 32;
 constexpr int FT_HALO = 2048;                  // bytes after the tile that are staged as well
 constexpr int FT_WIN = FT_TILE + FT_HALO;
 constexpr int FT_WORDS = FT_WIN / 64;          // 64-bit bitmap words
-constexpr int FT_PCAP = FT_TILE * 3 / 16;      // listed line ends per window: records down to ~22 bytes stay on the fast path
+#ifndef QUADE_F_PCAP
+#define QUADE_F_PCAP (FT_TILE * 3 / 32)
+#endif
+constexpr int FT_PCAP = QUADE_F_PCAP;          // listed line ends per window: files whose lines average >= 10.7 bytes (records >= 43) stay
+                                               // on the fast path, and 5 CTAs fit an SM: 0.377 -> 0.349 ms against twice the list at 4 CTAs
 constexpr uint32_t FT_NONE = 0xffffffffu;
 static_assert(FT_HALO / 64 == 32, "the halo's bitmap words are scanned by one warp");
 static_assert(FT_NW >= 2 && FT_NW <= 32 && FT_WIN < 65536, "line ends are listed as u16 window offsets");
-static_assert(FT_WPT == 1 || FT_WPT == 2, "the line-end counts of a thread's words share one register in the scans");
+constexpr int FT_NPK = (FT_WPT + 1) / 2;       // registers that carry the line-end counts of a thread's words through the scans
+static_assert(FT_WPT >= 1 && FT_WPT <= 4 && FT_NPK * FT_NW <= 32, "warp counts live in the first misc words");
 #ifndef QUADE_F_POLL1
 #define QUADE_F_POLL1 0                        // one lane per warp spins on the copy's mbarrier: measured slower (0.504 vs 0.477 ms)
 #endif
@@ -51,14 +56,14 @@ static_assert(FT_WPT == 1 || FT_WPT == 2, "the line-end counts of a thread's wor
 #define QUADE_F_IDXTOK 0                       // index reads: full name token scan (only "is there a token" is needed)
 #endif
 #ifndef QUADE_F_MINB
-#define QUADE_F_MINB 4                         // as many CTAs as the shared memory of an SM holds (32 KiB tiles)
+#define QUADE_F_MINB 5                         // as many CTAs as the shared memory of an SM holds (32 KiB tiles): 40 warps, 48 registers
 #endif
 
 // shared memory of a CTA: window (+ slack for the 64-byte header scan) | newline bitmap | line-end list | misc
-constexpr int FT_OFF_BM = FT_WIN + 128;
-constexpr int FT_OFF_POS = FT_OFF_BM + FT_WORDS * 8;
-constexpr int FT_OFF_MISC = FT_OFF_POS + FT_PCAP * 2;
-constexpr int FT_SMEM = FT_OFF_MISC + 256;
+constexpr int FT_OFF_POS = FT_WIN + 128;                        // u16[FT_PCAP] + a dump entry
+constexpr int FT_OFF_MISC = FT_OFF_POS + FT_PCAP * 2 + 16;
+constexpr int FT_OFF_BM = FT_OFF_MISC + 256;                    // redo pass only
+constexpr int FT_SMEM_FAST = FT_OFF_BM, FT_SMEM_REDO = FT_OFF_BM + FT_WORDS * 8;
 // misc (u32 index): [0..FT_NW) warp line-end counts, then
 enum { FM_HALO = 32, FM_BASE, FM_NINV, FM_BLANK, FM_BAD, FM_TK = 40 /* [2][4]: ticket, stream, tile in stream */, FM_BAR = 56 /* byte 224 */ };
 
@@ -472,18 +477,27 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             for (int w = 0; w < FT_WPT; ++w) mine[w] = s_bm[tid + w * FT_NT];
         }
 
-        // 2. line ends per thread; ONE warp scan for all words of a thread: their counts (<= 64 each, <= 2^14 per tile
-        //    and word row) travel as 16-bit fields of one register.  Redo pass: the halo's 32 words by warp 1
-        uint32_t cnt = 0u;
+        // 2. line ends per thread; the counts of a thread's words (<= 64 each, <= 2^14 per tile and word row) travel
+        //    through the scans as 16-bit fields, two per register.  Redo pass: the halo's 32 words by warp 1
+        uint32_t cnt[FT_NPK], inc[FT_NPK];
 #pragma unroll
-        for (int w = 0; w < FT_WPT; ++w) cnt |= (uint32_t)__popcll(mine[w]) << (16 * w);
-        uint32_t inc = cnt;
+        for (int k = 0; k < FT_NPK; ++k) {
+            cnt[k] = (uint32_t)__popcll(mine[2 * k]);
+            if (2 * k + 1 < FT_WPT) cnt[k] |= (uint32_t)__popcll(mine[2 * k + 1 < FT_WPT ? 2 * k + 1 : 0]) << 16;
+            inc[k] = cnt[k];
+        }
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t x = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += x;
+#pragma unroll
+            for (int k = 0; k < FT_NPK; ++k) {
+                const uint32_t x = __shfl_up_sync(0xffffffffu, inc[k], o);
+                if (lane >= o) inc[k] += x;
+            }
         }
-        if (lane == 31) s_misc[warp] = inc;
+        if (lane == 31) {
+#pragma unroll
+            for (int k = 0; k < FT_NPK; ++k) s_misc[FT_NPK * warp + k] = inc[k];
+        }
         u64 hm = 0;
         uint32_t hinc = 0, hcnt = 0;
         if (REDO && warp == 1) {
@@ -499,19 +513,23 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         }
         __syncthreads();                                        // B2: warp counts
         uint32_t before[FT_WPT], total = 0u;                    // line ends of the tile before each of the thread's words
-        {                                                       // exclusive prefix over the warps, by every warp
-            const uint32_t w = lane < FT_NW ? s_misc[lane] : 0u;
+#pragma unroll
+        for (int k = 0; k < FT_NPK; ++k) {                      // exclusive prefix over the warps, by every warp
+            const uint32_t w = lane < FT_NW ? s_misc[FT_NPK * lane + k] : 0u;
             uint32_t wi = w;
 #pragma unroll
             for (int o = 1; o < FT_NW; o <<= 1) {
                 const uint32_t x = __shfl_up_sync(0xffffffffu, wi, o);
                 if (lane >= o) wi += x;
             }
-            const uint32_t bw = __shfl_sync(0xffffffffu, wi - w, warp) + inc - cnt, tw = __shfl_sync(0xffffffffu, wi, FT_NW - 1);
+            const uint32_t bw = __shfl_sync(0xffffffffu, wi - w, warp) + inc[k] - cnt[k], tw = __shfl_sync(0xffffffffu, wi, FT_NW - 1);
 #pragma unroll
-            for (int w2 = 0; w2 < FT_WPT; ++w2) {               // word row w2 lies after all of the rows before it
-                before[w2] = total + ((bw >> (16 * w2)) & 0xffffu);
-                total += (tw >> (16 * w2)) & 0xffffu;
+            for (int j = 0; j < 2; ++j) {                       // word row w2 lies after all of the rows before it
+                const int w2 = 2 * k + j;
+                if (w2 < FT_WPT) {
+                    before[w2] = total + ((bw >> (16 * j)) & 0xffffu);
+                    total += (tw >> (16 * j)) & 0xffffu;
+                }
             }
         }
         // the fast pass needs the halo only for the record that starts last in the tile: 4 line ends at most
@@ -542,16 +560,34 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                 hi_[2 * w + 1] = before[w] + (uint32_t)__popc(hb[2 * w]);
                 any |= hb[2 * w] | hb[2 * w + 1];
             }
-            while (any) {
-                any = 0u;
+            if (REDO) {
+                while (any) {
+                    any = 0u;
 #pragma unroll
-                for (int h = 0; h < 2 * FT_WPT; ++h) {
-                    if (hb[h]) {
-                        const uint32_t bit = (uint32_t)__ffs((int)hb[h]) - 1u;
-                        hb[h] &= hb[h] - 1u;
+                    for (int h = 0; h < 2 * FT_WPT; ++h) {
+                        if (hb[h]) {
+                            const uint32_t bit = (uint32_t)__ffs((int)hb[h]) - 1u;
+                            hb[h] &= hb[h] - 1u;
+                            const uint32_t o0 = 64u * ((uint32_t)tid + (uint32_t)((h >> 1) * FT_NT)) + 32u * (uint32_t)(h & 1);
+                            if (hi_[h] < (uint32_t)FT_PCAP) s_pos[hi_[h]] = (uint16_t)(o0 + bit);
+                            ++hi_[h];
+                            any |= hb[h];
+                        }
+                    }
+                }
+            } else {
+                // branch-free body: a half without line ends stores to a dump slot behind the list (68 -> ~40
+                // instructions per iteration against the branchy form)
+                while (any) {
+                    any = 0u;
+#pragma unroll
+                    for (int h = 0; h < 2 * FT_WPT; ++h) {
+                        const uint32_t x = hb[h];
                         const uint32_t o0 = 64u * ((uint32_t)tid + (uint32_t)((h >> 1) * FT_NT)) + 32u * (uint32_t)(h & 1);
-                        if (!REDO || hi_[h] < (uint32_t)FT_PCAP) s_pos[hi_[h]] = (uint16_t)(o0 + bit);
-                        ++hi_[h];
+                        const uint32_t pos = o0 + (uint32_t)__ffs((int)x) - 1u;
+                        sts16(a_pos + 2u * (x ? hi_[h] : (uint32_t)FT_PCAP), pos);
+                        hi_[h] += x ? 1u : 0u;
+                        hb[h] = x & (x - 1u);
                         any |= hb[h];
                     }
                 }

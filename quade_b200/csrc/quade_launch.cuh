@@ -16,9 +16,9 @@ static void init_launch_config()
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaFuncSetAttribute(k_frame<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM);
-    cudaFuncSetAttribute(k_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_frame, k_frame<false>, FT_NT, FT_SMEM);
+    cudaFuncSetAttribute(k_frame<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM_FAST);
+    cudaFuncSetAttribute(k_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM_REDO);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_frame, k_frame<false>, FT_NT, FT_SMEM_FAST);
     if (g_occ_frame < 1) g_occ_frame = 1;
     cudaFuncSetAttribute(k_compact, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C3_SMEM * C3_WPC));
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact, k_compact, 32 * C3_WPC, C3_SMEM * C3_WPC);
@@ -33,7 +33,7 @@ void launch_frame(const BatchDev &b, cudaStream_t s)
     if (!total) return;
     uint32_t g = (uint32_t)(g_sms * (g_f_ctas > 0 && g_f_ctas < g_occ_frame ? g_f_ctas : g_occ_frame));
     if (g > total) g = total;
-    k_frame<false><<<g, FT_NT, FT_SMEM, s>>>(b, total);
+    k_frame<false><<<g, FT_NT, FT_SMEM_FAST, s>>>(b, total);
 }
 
 // tile scan + record -> scratch table, redo pass, files with invalid records
@@ -45,7 +45,7 @@ void launch_fix(const BatchDev &b, cudaStream_t s)
     uint32_t max_tiles = 0;
     for (int i = 0; i < b.n_streams; ++i) max_tiles = max(max_tiles, b.st[i].n ? b.st[i].n / (uint32_t)FT_TILE + 1u : 0u);
     k_tilescan<<<dim3((max_tiles + kTileChunk - 1) / kTileChunk, b.n_streams), kTileChunk, 0, s>>>(b);
-    k_frame<true><<<(uint32_t)g_sms, FT_NT, FT_SMEM, s>>>(b, total);
+    k_frame<true><<<(uint32_t)g_sms, FT_NT, FT_SMEM_REDO, s>>>(b, total);
     k_locate_rare<<<b.n_streams, kTileChunk, 0, s>>>(b);
 }
 
