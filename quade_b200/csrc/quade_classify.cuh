@@ -117,8 +117,26 @@ __global__ void __launch_bounds__(C2T) k_classify(const __grid_constant__ BatchD
         const uint32_t p0 = blk * b.pairs_per_block;
         uint32_t end = p0 + b.pairs_per_block;
         if (end > n_pairs) end = n_pairs;
-        for (uint32_t p = p0 + tid; p < end; p += C2T) {
-            const uint32_t v1 = i1.loc[p], v2 = b.dual ? i2.loc[p] : 0u;
+        // the scratch positions of the pair after this one are loaded while this one is classified: the chain
+        // loc -> record is two dependent global loads
+        uint32_t p = p0 + tid;
+        uint32_t nv1 = 0u, nv2 = 0u, nr1 = 0u, nr2 = 0u;
+        if (p < end) {
+            nv1 = i1.loc[p];
+            nv2 = b.dual ? i2.loc[p] : 0u;
+            nr1 = b.st[0].loc[p];
+            nr2 = b.st[1].loc[p];
+        }
+        for (; p < end; p += C2T) {
+            const uint32_t v1 = nv1, v2 = nv2, r1 = nr1, r2 = nr2;
+            if (p + C2T < end) {
+                nv1 = i1.loc[p + C2T];
+                nv2 = b.dual ? i2.loc[p + C2T] : 0u;
+                nr1 = b.st[0].loc[p + C2T];
+                nr2 = b.st[1].loc[p + C2T];
+            }
+            // insert-read fields for the output lengths (read even when the bin's writer is off: no dependent wait)
+            const uint32_t a1 = b.st[0].nv[r1].x + 2u * b.st[0].rec[r1].w, a2 = b.st[1].nv[r2].x + 2u * b.st[1].rec[r2].w;
             const uint4 d1 = i1.rec[v1];
             const uint4 d2 = b.dual ? i2.rec[v2] : make_uint4(0, 0, 0, 0);
             const uint32_t in1 = d1.w & 0xffu, mn1 = (d1.w >> 8) & 0xffu, in2 = d2.w & 0xffu, mn2 = (d2.w >> 8) & 0xffu;
@@ -206,9 +224,8 @@ __global__ void __launch_bounds__(C2T) k_classify(const __grid_constant__ BatchD
             }
             uint32_t l1 = 0, l2 = 0;
             if (wr) {
-                const uint32_t r1 = b.st[0].loc[p], r2 = b.st[1].loc[p];
-                l1 = b.st[0].nv[r1].x + suf_len + 2u * b.st[0].rec[r1].w + 5u;
-                l2 = b.st[1].nv[r2].x + suf_len + 2u * b.st[1].rec[r2].w + 5u;
+                l1 = a1 + suf_len + 5u;
+                l2 = a2 + suf_len + 5u;
                 atomicAdd(&h_b1[bin], l1);
                 atomicAdd(&h_b2[bin], l2);
             }

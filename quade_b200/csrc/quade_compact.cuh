@@ -159,13 +159,17 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
 
     // per-pair metadata of a tile.  load_raw only ISSUES the global loads (nothing consumes them), so that the
     // loads of the next tile fly during this tile's phases; finish_meta turns them into the staged spans.
-    auto load_raw = [&](uint32_t tile, TileMeta &m) {
+    // the scratch position of a record is read one tile earlier still: two dependent loads, each a tile ahead
+    auto load_loc = [&](uint32_t tile) -> uint32_t {
+        const uint32_t p = tile * tp + pr;
+        return rec_lane && tile < n_tiles && p < n_pairs ? b.st[k].loc[p] : 0u;
+    };
+    auto load_raw = [&](uint32_t tile, TileMeta &m, uint32_t v) {
         const uint32_t p = tile * tp + pr;
         m.rc = make_uint4(0, 0, 0, 0);
         m.nlen = m.cls = m.ooff = 0u;
         m.suf0 = m.suf1 = make_uint4(0, 0, 0, 0);
         if (rec_lane && tile < n_tiles && p < n_pairs) {
-            const uint32_t v = b.st[k].loc[p];                          // scratch position of the pair's record
             m.cls = b.cls[p];
             m.rc = b.st[k].rec[v];
             m.nlen = b.st[k].nv[v].x;
@@ -218,8 +222,9 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
     uint32_t phase_bits = 0;
     uint32_t tile = first_tile, it = 0;
     TileMeta cur, nxt;
+    uint32_t v_next = load_loc(tile + tile_stride);
     if (tile < n_tiles) {
-        load_raw(tile, cur);
+        load_raw(tile, cur, load_loc(tile));
         finish_meta(cur);
         issue(cur, 0);
     }
@@ -227,7 +232,8 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
     for (; tile < n_tiles; tile += tile_stride, ++it) {
         const uint32_t stage = C3_STAGES == 2 ? (it & 1u) : 0u;
         const uint32_t ntile = tile + tile_stride;
-        load_raw(ntile, nxt);                                          // loads only; consumed at the end of the iteration
+        load_raw(ntile, nxt, v_next);                                  // loads only; consumed at the end of the iteration
+        v_next = load_loc(ntile + tile_stride);
         if (C3_STAGES == 2 && ntile < n_tiles) {
             finish_meta(nxt);
             issue(nxt, stage ^ 1u);
