@@ -42,6 +42,10 @@ def parse_args():
     ap.add_argument("--pairs", type=int, default=2_000_000, help="read pairs per step per GPU")
     ap.add_argument("--min-qual", type=int, default=None)
     ap.add_argument("--cpu-pairs", type=int, default=1_000_000, help="sample size of the CPU baseline leg")
+    ap.add_argument("--ref-pairs", type=int, default=8_000, help="pairs per process and step of the reference-Python legs")
+    ap.add_argument("--distinct", type=int, default=0,
+                    help="distinct device-generated chunks the steps cycle through (0 = one per step incl. warm-up, capped by --distinct-gb)")
+    ap.add_argument("--distinct-gb", type=float, default=48.0, help="HBM budget for the resident input chunks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--slots", type=int, default=6,
@@ -54,9 +58,9 @@ def parse_args():
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full summary
-    of this same command (profiles/r01_traffic.json, written by tools/ncu_traffic.py); None if absent."""
+    of this same command (profiles/r02_traffic.json, written by tools/ncu_traffic.py); None if absent."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as fh:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as fh:
             return json.load(fh)["kernels"][kernel]["dram_bytes_per_launch"]
     except Exception:
         return None
@@ -119,7 +123,8 @@ class ClockSampler(threading.Thread):
 
 
 class CpuLeg:
-    """The CPU restatement of the reference path (oracle/, C, one chunk per thread) on a bounded sample."""
+    """The C restatement of the reference path (oracle/quade_oracle.c, one chunk per thread) on a bounded sample:
+    kind "port"."""
 
     def __init__(self, synth, min_qual, n_pairs, threads):
         from oracle import oracle as O
@@ -139,31 +144,125 @@ class CpuLeg:
                 "(oracle/quade_oracle.c), inputs and outputs in RAM" % (self.n_chunks, self.per))
 
 
+class RefLeg:
+    """The reference's OWN code (a-slide/Quade src/*.py, unmodified on disk under oracle/_ref, run under Python 3 by
+    oracle/ref_shim.py) on a bounded sample: `procs` independent single-threaded processes, one chunk of `per`
+    pairs each, plain FASTQ in, fastq.gz out, local scratch.  The clock is the reference's own `Done in` line
+    (src/Quade.py:172,192); a step takes as long as its slowest process.  kind "reference"."""
+
+    def __init__(self, synth, min_qual, per, procs):
+        import tempfile
+        from oracle import ref_shim
+        if not ref_shim.available():
+            raise RuntimeError("reference sources not found (oracle/make_ref.py copies them to oracle/_ref)")
+        self.per, self.procs = per, procs
+        self.root = tempfile.mkdtemp(prefix="quade_ref_")
+        self.dirs = []
+        for c in range(procs):
+            d = os.path.join(self.root, "p%02d" % c)
+            os.makedirs(d)
+            arrays = synth.generate(c * per, per)
+            names = []
+            for k, a in enumerate(arrays):
+                fn = os.path.join(d, "in_%d.fastq" % k)
+                a.tofile(fn)
+                names.append([fn])
+            with open(os.path.join(d, "conf.txt"), "w") as fh:
+                fh.write(synth.conf_text(names, min_qual))
+            self.dirs.append(d)
+
+    def run(self):
+        """One step: every process demultiplexes its chunk once.  Returns (pairs, seconds)."""
+        env = dict(os.environ, PYTHONPATH=ROOT)
+        ps = [subprocess.Popen([sys.executable, "-m", "oracle.ref_shim", os.path.join(d, "conf.txt")], cwd=d, env=env,
+                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for d in self.dirs]
+        worst = 0.0
+        for p in ps:
+            out, _ = p.communicate()
+            secs = None
+            for line in out.splitlines():
+                if line.startswith("Done in ") and line.endswith("s"):
+                    secs = float(line[len("Done in "):-1])
+            if p.returncode != 0 or secs is None:
+                raise RuntimeError("the reference failed:\n" + out[-2000:])
+            worst = max(worst, secs)
+        return self.per * self.procs, worst
+
+    def close(self):
+        import shutil
+        shutil.rmtree(self.root, ignore_errors=True)
+
+    def describe(self):
+        return ("%d process(es) x %d pairs, the reference's own Python (oracle/_ref, %s through oracle/ref_shim.py), one "
+                "thread each, plain FASTQ in, fastq.gz out, its own 'Done in' clock" % (
+                    self.procs, self.per, "python%d.%d" % sys.version_info[:2]))
+
+
+def host_info():
+    model = "?"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return {"nproc": os.cpu_count() or 1, "cpu_model": model}
+
+
+def workload_config(args, synth, min_qual, sizes):
+    """The `config` object: the workload only, the same for both arms."""
+    return {"workload": WORKLOADS[args.config], "config": args.config, "pairs_per_step_per_gpu": args.pairs,
+            "min_qual": min_qual,
+            "l2": "inputs (%.0f MB per step) larger than the 126 MB L2" % (sum(sizes) / 1e6),
+            "parallelism": "chunks sharded over %d GPU(s), counters all-reduced (NCCL)" % args.gpus}
+
+
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU algorithm on the host cores (oracle port; the reference itself is
-    Python 2.7 and /root/reference does not exist on the GPU box).  Rank 0 only."""
+    """--impl reference: the reference's own CPU implementation on the host cores.  The reference is pure Python
+    and single-threaded, so "all the host threads it can use" is one independent process per core, each on its own
+    chunk (src/Quade.py:198-206: chunks are independent).  Falls back to the C port only if oracle/_ref is absent.
+    Rank 0 only; nothing of the product library is loaded here."""
     if rank != 0:
         return
     from quade_b200.synth import Synth
+    from oracle import ref_shim
     synth = Synth.from_config(args.config)
     min_qual = synth.min_qual if args.min_qual is None else args.min_qual
     cores = os.cpu_count() or 1
-    sample = min(args.pairs, max(100_000, args.cpu_pairs))
+    sizes = synth.sizes(0, args.pairs)
+    port_leg = CpuLeg(synth, min_qual, min(args.pairs, max(100_000, args.cpu_pairs)), cores)
+    port_leg.run()
+    pp, ps = port_leg.run()
+    port = {"value": pp / ps, "unit": UNIT, "cores": cores, "kind": "port", "sample": port_leg.describe()}
     times, pairs_done = [], 0
-    leg = CpuLeg(synth, min_qual, sample, cores)
-    for it in range(args.warmup + args.steps):
-        pairs, secs = leg.run()
-        if it >= args.warmup:
-            times.append(secs)
-            pairs_done += pairs
+    if ref_shim.available():
+        leg = RefLeg(synth, min_qual, args.ref_pairs, cores)
+        try:
+            for it in range(args.warmup + args.steps):
+                pairs, secs = leg.run()
+                if it >= args.warmup:
+                    times.append(secs)
+                    pairs_done += pairs
+        finally:
+            leg.close()
+        kind, sample = "reference", leg.describe() + " per step"
+    else:
+        leg = port_leg
+        for it in range(args.warmup + args.steps):
+            pairs, secs = leg.run()
+            if it >= args.warmup:
+                times.append(secs)
+                pairs_done += pairs
+        kind, sample = "port", leg.describe() + " per step (oracle/_ref absent: reference sources were not materialised)"
     total = sum(times)
     value = pairs_done / total
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * total / max(1, args.steps), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "impl": "reference",
-            "config": {"workload": WORKLOADS[args.config], "config": args.config, "pairs_per_step": leg.n_chunks * leg.per},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": leg.describe() + " per step"},
+            "config": workload_config(args, synth, min_qual, sizes),
+            "cpu_baseline": dict({"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}, **host_info()),
+            "cpu_baseline_port": port,
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
@@ -183,18 +282,23 @@ def run_ours(args, rank, world, local_rank):
     min_qual = synth.min_qual if args.min_qual is None else args.min_qual
     P, ns = args.pairs, synth.n_streams
 
-    # this rank's chunk: pairs [rank*P, rank*P + P) of the data set, generated into pinned host buffers
-    sizes = synth.sizes(rank * P, P)
-    pinned = [PinnedBuffer(n) for n in sizes]
-    threads = max(1, (os.cpu_count() or 1) // world)
-    synth.fill(rank * P, P, [b.array for b in pinned], n_threads=min(64, threads))
-    dev_in = [torch.empty(n + 64, dtype=torch.uint8, device=dev) for n in sizes]
-    for t, b in zip(dev_in, pinned):
-        t[:b.nbytes].copy_(torch.from_numpy(b.array), non_blocking=False)
-    ctx = DemuxContext(synth.dual, synth.spans(), min_qual, synth.sample_keys(), device=local_rank,
-                       max_stream_bytes=max(sizes) + 4096, max_pairs=P + 1024, max_records=P + P // 8, n_slots=args.slots)
+    # ---- inputs of `value`: D DISTINCT chunks of P pairs, generated in HBM by the device-side generator (the bytes
+    # are those of the host generator: tests/test_gpu_parity.py).  Rank r owns chunks r*D .. r*D + D - 1 of the data set.
+    sizes0 = synth.sizes(rank * P, P)
+    D = args.distinct or (args.steps + args.warmup)
+    D = max(1, min(D, int(args.distinct_gb * 1e9 // max(1, sum(sizes0)))))
+    chunks = []
+    for j in range(D):
+        first = (rank * D + j) * P
+        sz = synth.sizes(first, P)
+        bufs = [torch.empty(n + 64, dtype=torch.uint8, device=dev) for n in sz]
+        got = synth.fill_device(first, P, [t.data_ptr() for t in bufs])
+        assert got == sz, (got, sz)
+        chunks.append(([t.data_ptr() for t in bufs], sz, bufs))
+    cap = max(max(c[1]) for c in chunks) + 4096
+    ctx = DemuxContext(synth.dual, synth.spans(), min_qual, synth.sample_keys(), device=local_rank, max_stream_bytes=cap,
+                       max_pairs=P + 1024, max_records=P + P // 8, n_slots=args.slots, device_only=True)
     stream = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
-    ptrs = [t.data_ptr() for t in dev_in]
 
     def barrier():
         if world > 1:
@@ -203,8 +307,8 @@ def run_ours(args, rank, world, local_rank):
 
     diag = []                                              # (seconds, what) of every host call, QUADE_BENCH_DIAG=1
 
-    def device_steps(n):
-        """n batches back to back, args.slots in flight; returns the collected results."""
+    def device_steps(n, start=0):
+        """n batches back to back, args.slots in flight, step i on chunk (start + i) mod D; returns the results."""
         res = []
         for i in range(n):
             if ctx.in_flight == args.slots:
@@ -212,16 +316,17 @@ def run_ours(args, rank, world, local_rank):
                 res.append(ctx.collect())
                 diag.append((time.perf_counter() - t, "collect"))
             t = time.perf_counter()
-            ctx.submit_device(ptrs, sizes, last=True, ticket=i)
+            ptrs, sz, _ = chunks[(start + i) % D]
+            ctx.submit_device(ptrs, sz, last=True, ticket=i)
             diag.append((time.perf_counter() - t, "submit"))
         while ctx.in_flight:
             res.append(ctx.collect())
         return res
 
     # ---- value: HBM-resident inputs, kernels only --------------------------------------------------------
-    def timed_block(n):
+    def timed_block(n, start=0):
         """What the timed region runs: n steps, then the report counters summed over the ranks."""
-        res = device_steps(n)
+        res = device_steps(n, start)
         cnt = torch.from_numpy(ctx.counters()).to(dev)
         if world > 1:
             dist.all_reduce(cnt)           # the path's only collective: the report counters (NCCL)
@@ -234,12 +339,13 @@ def run_ours(args, rank, world, local_rank):
         device_steps(4)                    # no collective here: the number of rounds is wall-clock bound per rank
     barrier()
     timed_block(args.warmup)
+    ctx.reset_counters()
     barrier()
     sampler.begin()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
     del diag[:]
-    results, counters = timed_block(args.steps)
+    results, counters = timed_block(args.steps, args.warmup)
     ev1.record(stream)
     if os.environ.get("QUADE_BENCH_DIAG"):
         print("diag: slowest host calls in the timed region (ms):",
@@ -251,18 +357,21 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_total = float(t.item())
-    r0 = results[-1]
     assert all(r.n_pairs == P for r in results), "a batch did not demultiplex every pair"
     launches = sum(r.gpu_launches for r in results)
+    reframed = sum(r.reframed_tiles for r in results)
     value = world * P * args.steps / (ms_total * 1e-3)
 
     # ---- roofline of the dominant kernel (CUDA events on the compute stream, averaged over the timed steps) --
-    kms = {k: sum(r.ms_kernel[k] for r in results) / len(results) for k in _lib.K_NAMES}
-    in_bytes, out_bytes = r0.in_bytes, r0.out_bytes
-    insert_in = sizes[0] + sizes[1]
-    alg = {"frame": in_bytes, "compact": insert_in + out_bytes, "classify": sum(sizes[2:])}
+    nres = len(results)
+    kms = {k: sum(r.ms_kernel[k] for r in results) / nres for k in _lib.K_NAMES}
+    in_bytes = sum(r.in_bytes for r in results) / nres
+    out_bytes = sum(r.out_bytes for r in results) / nres
+    insert_in = sum(chunks[(args.warmup + i) % D][1][0] + chunks[(args.warmup + i) % D][1][1] for i in range(args.steps)) / args.steps
+    index_in = in_bytes - insert_in
+    alg = {"frame": in_bytes, "compact": insert_in + out_bytes, "classify": index_in}
     dom = max(("frame", "compact", "classify"), key=lambda k: kms[k])
-    kname = {"frame": "k_frame6", "compact": "k_compact3", "classify": "k_classify2"}[dom]
+    kname = {"frame": "k_frame", "compact": "k_compact", "classify": "k_classify"}[dom]
     peak, peak_src = peaks()
     ach = alg[dom] / (kms[dom] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": kname, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
@@ -273,24 +382,38 @@ def run_ours(args, rank, world, local_rank):
                 "pipeline": {"algorithmic_bytes_per_step": in_bytes + out_bytes,
                              "achieved": (in_bytes + out_bytes) * args.steps / (ms_total * 1e-3) / 1e9,
                              "frac": (in_bytes + out_bytes) * args.steps / (ms_total * 1e-3) / 1e9 / peak}}
+    und = int(counters[0].item())
+    tot = int(counters.sum().item())
+    ctx.close()
+    del chunks
+    torch.cuda.empty_cache()
 
     # ---- e2e: pinned host buffers -> quade_submit (H2D) -> kernels -> quade_collect (D2H), double-buffered --
     e2e = None
     if not args.no_e2e:
+        e_slots = min(args.slots, 3)                           # PCIe-bound: a deeper ring only adds pinned memory
+        pinned = [PinnedBuffer(n) for n in sizes0]
+        threads = max(1, (os.cpu_count() or 1) // world)
+        synth.fill(rank * P, P, [b.array for b in pinned], n_threads=min(64, threads))
         host = [b.array for b in pinned]
+        ectx = DemuxContext(synth.dual, synth.spans(), min_qual, synth.sample_keys(), device=local_rank,
+                            max_stream_bytes=max(sizes0) + 4096, max_pairs=P + 1024, max_records=P + P // 8, n_slots=e_slots)
+        e_out = [0]
 
         def host_steps(n):
             done = 0
             for i in range(n):
-                if ctx.in_flight == min(args.slots, 3):                # PCIe-bound: a deeper ring only adds pinned memory
-                    r = ctx.collect()
+                if ectx.in_flight == e_slots:
+                    r = ectx.collect()
                     done += int(r.arena(0)[-1]) * 0 + r.n_pairs      # touches the copied-back result
-                ctx.submit(host, last=True, ticket=i)
-            while ctx.in_flight:
-                r = ctx.collect()
+                    e_out[0] = r.out_bytes
+                ectx.submit(host, last=True, ticket=i)
+            while ectx.in_flight:
+                r = ectx.collect()
                 done += int(r.arena(1)[-1]) * 0 + r.n_pairs
+                e_out[0] = r.out_bytes
             return done
-        host_steps(max(args.slots + 1, args.warmup))           # every slot's pinned output arena exists before timing
+        host_steps(max(e_slots + 1, args.warmup))
         barrier()
         t0 = time.perf_counter()
         done = host_steps(args.steps)
@@ -301,38 +424,47 @@ def run_ours(args, rank, world, local_rank):
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         assert done == P * args.steps
         e2e = {"value": world * P * args.steps / float(tt.item()), "unit": UNIT,
-               "h2d_bytes_per_step": int(sum(sizes)), "d2h_bytes_per_step": int(out_bytes),
+               "h2d_bytes_per_step": int(sum(sizes0)), "d2h_bytes_per_step": int(e_out[0]),
                "timing": "wall clock between device synchronisations, max over ranks",
-               "pcie_GBps_per_gpu": (sum(sizes) + out_bytes) * args.steps / float(tt.item()) / 1e9}
+               "pcie_GBps_per_gpu": (sum(sizes0) + e_out[0]) * args.steps / float(tt.item()) / 1e9}
+        ectx.close()
 
-    # ---- CPU baseline: rank 0, N=1 only ---------------------------------------------------------------------
-    cpu = None
+    # ---- CPU baseline: rank 0, N=1 only: the reference's own Python on one core; the C port on all cores beside it --
+    cpu = port = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import ref_shim
         cores = os.cpu_count() or 1
         leg = CpuLeg(synth, min_qual, min(args.cpu_pairs, P), cores)
         leg.run()
         reps, secs, pairs = 0, 0.0, 0
-        while secs < 5.0 and reps < 20:
+        while secs < 3.0 and reps < 20:
             pr, sc = leg.run()
             pairs, secs, reps = pairs + pr, secs + sc, reps + 1
-        cpu = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": leg.describe() + ", %d repetitions" % reps}
+        port = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": "port",
+                "sample": leg.describe() + ", %d repetitions" % reps}
+        if ref_shim.available():
+            rleg = RefLeg(synth, min_qual, 2 * args.ref_pairs, 1)
+            try:
+                rleg.run()
+                pr, sc = rleg.run()
+            finally:
+                rleg.close()
+            cpu = dict({"value": pr / sc, "unit": UNIT, "cores": 1, "kind": "reference", "sample": rleg.describe()}, **host_info())
+        else:
+            cpu = dict(port, **host_info())
 
     if rank == 0:
-        und = int(counters[0].item())
-        tot = int(counters.sum().item())
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u8", "data": "synthetic",
-                "config": {"workload": WORKLOADS[args.config], "config": args.config, "pairs_per_step_per_gpu": P,
-                           "min_qual": min_qual, "in_bytes_per_pair": in_bytes / P, "out_bytes_per_pair": out_bytes / P,
-                           "l2": "inputs (%.0f MB per step) larger than the 126 MB L2" % (in_bytes / 1e6),
-                           "parallelism": "chunks sharded over %d GPU(s), counters all-reduced (NCCL)" % world,
-                           "undetermined_frac": und / max(1, tot)},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+                "config": workload_config(args, synth, min_qual, sizes0),
+                "workload_stats": {"in_bytes_per_pair": in_bytes / P, "out_bytes_per_pair": out_bytes / P,
+                                   "undetermined_frac": und / max(1, tot), "distinct_chunks_per_gpu": D,
+                                   "inputs": "generated in HBM by the device-side generator, step i on chunk i mod %d" % D,
+                                   "reframed_tiles_per_step": reframed / nres},
+                "roofline": roofline, "cpu_baseline": cpu, "cpu_baseline_port": port, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clocks}
         emit(line)
-    ctx.close()
 
 
 _JSON_OUT = None

@@ -140,28 +140,6 @@ int quade_counters_reset(quade_ctx *ctx);
 /* CUDA stream handle (cudaStream_t) kernels are launched on, for callers that time with their own events */
 int quade_compute_stream(quade_ctx *ctx, void **stream);
 
-/* --- synthetic dual/single-indexed paired-end data (SURVEY.md section 8(d) generator), host side -------------
- * Used by bench.py and the tests to make inputs; not part of the demultiplexing path. */
-typedef struct {
-    uint64_t seed;
-    int32_t dual;         /* 0: R1,R2,I1   1: R1,R2,I1,I2 */
-    int32_t read_len;     /* insert read length (150) */
-    int32_t index_len;    /* sample barcode bases per index read */
-    int32_t mol_len;      /* molecular bases following the barcode on each index read */
-    int32_t n_samples;
-    int32_t floor_mode;   /* 0: per-pair phred floor 30 w.p. 0.9 else 2;  1: floor uniform 2..40 */
-    double undetermined;  /* probability that the barcode is random */
-} quade_synth_params;
-
-/* barcodes: n_samples * index_len * (dual?2:1) bytes, pairwise Hamming distance >= 3 per index */
-int quade_synth_barcodes(const quade_synth_params *p, uint8_t *barcodes);
-/* sizes of the 4 streams for pairs [first, first+count) */
-int quade_synth_sizes(const quade_synth_params *p, const uint8_t *barcodes, uint64_t first, uint64_t count,
-                      uint64_t nbytes[4]);
-/* fill the streams (buffers sized by quade_synth_sizes) using n_threads host threads */
-int quade_synth_fill(const quade_synth_params *p, const uint8_t *barcodes, uint64_t first, uint64_t count,
-                     uint8_t *const stream[4], int n_threads);
-
 #ifdef __cplusplus
 }
 #endif

@@ -5,8 +5,8 @@ It is used (a) by `tests/golden/make_golden.py` to generate golden vectors from 
 code, and (b) by tests that cross-check the C oracle when `/root/reference` is present (it never is
 on the GPU box, so those tests skip there).
 
-No reference code is copied into this repository: the shim reads `/root/reference/src/*.py` as text at
-run time, applies the textual substitutions listed in SURVEY.md section 8(c) (Python 2 -> 3 spelling
+No reference code is committed to this repository: the shim reads `/root/reference/src/*.py` (or the git-ignored
+copy under `oracle/_ref/`, made by `oracle/make_ref.py` so that the sources reach the GPU box) as text at run time, applies the textual substitutions listed in SURVEY.md section 8(c) (Python 2 -> 3 spelling
 only, no behavioural change inside the ASCII FASTQ domain) and `exec`s the result into synthetic
 modules.  Substitutions:
 
@@ -30,7 +30,18 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("QUADE_REFERENCE_ROOT", "/root/reference")
+def _root():
+    """QUADE_REFERENCE_ROOT, else /root/reference (build container), else the copy oracle/make_ref.py left under
+    oracle/_ref (the GPU box)."""
+    env = os.environ.get("QUADE_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isfile("/root/reference/src/Quade.py"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _root()
 _SRC = os.path.join(REFERENCE_ROOT, "src")
 
 

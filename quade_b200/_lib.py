@@ -14,8 +14,7 @@ K_NAMES = ["frame", "tilescan", "pairing", "classify", "binscan", "offsets", "co
 K_COUNT = len(K_NAMES)
 SYMBOLS = ["quade_version", "quade_last_error", "quade_device_count", "quade_host_alloc", "quade_host_free",
            "quade_ctx_create", "quade_ctx_destroy", "quade_ctx_set_samples", "quade_submit", "quade_collect",
-           "quade_counters", "quade_counters_reset", "quade_compute_stream", "quade_synth_barcodes",
-           "quade_synth_sizes", "quade_synth_fill"]
+           "quade_counters", "quade_counters_reset", "quade_compute_stream"]
 
 
 class Params(C.Structure):
@@ -37,12 +36,6 @@ class Result(C.Structure):
                 ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
                 ("ms_kernel", C.c_float * K_COUNT), ("in_bytes", C.c_uint64), ("out_bytes", C.c_uint64),
                 ("gpu_launches", C.c_uint64), ("reframed_tiles", C.c_uint64)]
-
-
-class SynthParams(C.Structure):
-    _fields_ = [("seed", C.c_uint64), ("dual", C.c_int32), ("read_len", C.c_int32), ("index_len", C.c_int32),
-                ("mol_len", C.c_int32), ("n_samples", C.c_int32), ("floor_mode", C.c_int32),
-                ("undetermined", C.c_double)]
 
 
 class QuadeError(RuntimeError):
@@ -67,7 +60,7 @@ def lib():
     if _build.is_stale():
         _build.build()
     L = C.CDLL(path)
-    vp, u64p = C.c_void_p, C.POINTER(C.c_uint64)
+    vp = C.c_void_p
     L.quade_version.restype = C.c_int
     L.quade_last_error.restype = C.c_char_p
     L.quade_device_count.argtypes = [C.POINTER(C.c_int)]
@@ -81,9 +74,6 @@ def lib():
     L.quade_counters.argtypes = [vp, vp]
     L.quade_counters_reset.argtypes = [vp]
     L.quade_compute_stream.argtypes = [vp, C.POINTER(vp)]
-    L.quade_synth_barcodes.argtypes = [C.POINTER(SynthParams), vp]
-    L.quade_synth_sizes.argtypes = [C.POINTER(SynthParams), vp, C.c_uint64, C.c_uint64, u64p]
-    L.quade_synth_fill.argtypes = [C.POINTER(SynthParams), vp, C.c_uint64, C.c_uint64, C.POINTER(vp), C.c_int]
     for name in SYMBOLS:
         if name not in ("quade_version", "quade_last_error"):
             getattr(L, name).restype = C.c_int

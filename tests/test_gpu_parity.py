@@ -331,3 +331,59 @@ def test_long_reads_spanning_tiles_match_oracle(max_len):
     _assert_same(r, ref, p.nbins, "long reads %d" % max_len)
     assert r.n_pairs == n
     ctx.close()
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg3", "cfg4", "cfg5"])
+def test_device_generator_writes_the_bytes_of_the_host_generator(name):
+    """quade_synth_fill_device (CUDA kernels, HBM-resident buffers: what bench.py streams) == quade_synth_fill (host
+    threads: what the oracle is fed) for 1 M pairs starting in the middle of the data set."""
+    import torch
+    from quade_b200.synth import Synth
+    s = Synth.from_config(name)
+    first, n = 3_000_017, 1_000_000
+    host = s.generate(first, n)
+    sizes = [len(a) for a in host]
+    dev = [torch.zeros(x + 64, dtype=torch.uint8, device="cuda") for x in sizes]
+    assert s.fill_device(first, n, [t.data_ptr() for t in dev]) == sizes
+    for k in range(s.n_streams):
+        assert torch.equal(dev[k][:sizes[k]].cpu(), torch.from_numpy(host[k])), "stream %d" % k
+        assert int(dev[k][sizes[k]:].sum()) == 0, "the generator wrote past the end of stream %d" % k
+
+
+def _bin_checksums(arena, bin_off):
+    """per bin: (bytes, 64-bit running checksum of the byte stream: two CRC-32 with different seeds)"""
+    import zlib
+    out = []
+    mv = memoryview(arena)
+    for b in range(len(bin_off) - 1):
+        seg = mv[int(bin_off[b]):int(bin_off[b + 1])]
+        out.append((len(seg), zlib.crc32(seg) | zlib.crc32(seg, 0x9E3779B9) << 32))
+    return out
+
+
+def test_sampled_chunks_of_the_scale_config_match_the_oracle_by_checksum():
+    """BASELINE config 4 (dual 10+10, sharded over 8 GPUs, 2 B reads) cannot be compared byte for byte as a whole:
+    chunks sampled from the ranks' shares are generated ON THE DEVICE (as bench.py does), demultiplexed from HBM, and
+    compared with the oracle fed by the host generator through per-bin byte counts, a 64-bit running checksum per
+    bin and read, and the counter vector (SURVEY.md section 8(d) "parity at scale")."""
+    import torch
+    from quade_b200.synth import Synth
+    s = Synth.from_config("cfg4")
+    P = 500_000
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    ctx = None
+    for chunk in (0, 777, 3999):                                  # 4000 chunks x 500 k pairs = 2 B pairs
+        first = chunk * P
+        sizes = s.sizes(first, P)
+        if ctx is None:
+            ctx, _ = _ctx_for(p, max_stream_bytes=max(sizes) + (1 << 20), max_pairs=P + 1024, n_slots=1)
+        dev = [torch.empty(x + 64, dtype=torch.uint8, device="cuda") for x in sizes]
+        assert s.fill_device(first, P, [t.data_ptr() for t in dev]) == sizes
+        host_in = [t[:n].cpu().numpy() for t, n in zip(dev, sizes)]          # D2H of the device-made inputs
+        r = ctx.run(host_in, last=True)
+        ref = O.demux_batch(p, s.generate(first, P), last=True)
+        assert r.n_pairs == ref.n_pairs == P and (r.counters == ref.counters).all()
+        for k in range(2):
+            assert (r.bin_off[k] == ref.bin_off[k]).all()
+            assert _bin_checksums(r.arena(k), r.bin_off[k]) == _bin_checksums(np.frombuffer(ref.out[k], dtype=np.uint8), ref.bin_off[k])
+    ctx.close()
