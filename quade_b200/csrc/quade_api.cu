@@ -347,7 +347,7 @@ extern "C" int quade_ctx_set_samples(quade_ctx *c, const uint8_t *keys, const ui
                 return fail(QUADE_ERR_BAD_SAMPLE, "samples %d and %d share the same index", a, b2);
 
     uint32_t n_slots = 16, n_buckets = 4;
-    while (n_slots < 4u * (uint32_t)S) n_slots <<= 1;
+    while (n_slots < 2u * (uint32_t)S) n_slots <<= 1;   // load <= 50 %: 384 samples -> 16 KiB of table per k_classify CTA, 8 CTAs per SM
     while (n_buckets < (uint32_t)(S + 1) / 2) n_buckets <<= 1;
     std::vector<uint4> entries;
     std::vector<uint16_t> disp;
