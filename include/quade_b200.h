@@ -7,7 +7,7 @@
  *   quade_ctx_create        <- Quade.__init__ deriving flags/spans/min_qual          src/Quade.py:96-129
  *                              + Sample.CLASS_INIT(write_*, min_qual)                 src/Sample.py:48-54
  *   quade_ctx_set_samples   <- Sample.__init__ filling INDEX_TO_SAMPLE                src/Sample.py:132-153
- *   quade_submit / collect  <- one slice of the `while True` loop of
+ *   quade_submit/peek/collect <- one slice of the `while True` loop of
  *                              double_index_parser / simple_index_parser              src/Quade.py:195-254
  *                              = FastqReader x3/4                                     src/pyFastq/FastqReader.py:25-58
  *                              + FastqSeq slicing/concat                              src/pyFastq/FastqSeq.py:91-101
@@ -105,6 +105,9 @@ typedef struct {
     const int64_t *counters;   /* nbins pair counts of this batch (host memory) */
     int32_t nbins;
     int32_t err;               /* QUADE_OK or QUADE_ERR_BLANK_HEADER / QUADE_ERR_CAPACITY for this batch */
+    int32_t chunk_end;         /* 1: a file whose buffer ends at end-of-file has no further valid record -- the
+                                  reference's StopIteration, the chunk ends with this batch (src/Quade.py:223,252) */
+    int32_t reserved;
     float ms_h2d, ms_kernels, ms_d2h;     /* CUDA-event durations of the three legs */
     float ms_kernel[QUADE_K_COUNT];       /* per kernel stage, events on the compute stream */
     uint64_t in_bytes;         /* sum of consumed[] */
@@ -131,6 +134,11 @@ int quade_ctx_set_samples(quade_ctx *ctx, const uint8_t *keys, const uint32_t *k
 
 /* asynchronous: H2D copy (copy stream) -> kernels (compute stream); returns once everything is enqueued */
 int quade_submit(quade_ctx *ctx, const quade_batch *batch);
+/* blocks until the kernels of the oldest submitted batch are done and describes it -- n_pairs, consumed[], n_skipped[],
+ * bin_off, counters, errors; out[] stays NULL -- WITHOUT copying its bins back and without releasing it: the caller
+ * learns the carry-over (consumed[]) early, submits the next batch, and only then collects this one, so that the
+ * D2H copy of batch N runs beside the H2D copy and the kernels of batch N+1 */
+int quade_peek(quade_ctx *ctx, quade_result *res);
 /* blocks until the oldest submitted batch is done, copies its bins back (D2H stream) and describes them */
 int quade_collect(quade_ctx *ctx, quade_result *res);
 

@@ -25,7 +25,7 @@ class _Params(C.Structure):
 class _Result(C.Structure):
     _fields_ = [("out", C.c_void_p * 2), ("bin_off", C.c_void_p * 2), ("counters", C.c_void_p),
                 ("n_pairs", C.c_uint64), ("consumed", C.c_uint64 * 4), ("n_skipped", C.c_uint64 * 4),
-                ("nbins", C.c_int32), ("err", C.c_int32)]
+                ("nbins", C.c_int32), ("err", C.c_int32), ("chunk_end", C.c_int32), ("reserved", C.c_int32)]
 
 
 def build(force=False):
@@ -84,7 +84,8 @@ class OracleParams:
 
 
 class OracleResult:
-    def __init__(self, out, bin_off, counters, n_pairs, consumed, n_skipped):
+    def __init__(self, out, bin_off, counters, n_pairs, consumed, n_skipped, chunk_end=False):
+        self.chunk_end = chunk_end
         self.out = out              # [bytes R1 arena, bytes R2 arena]
         self.bin_off = bin_off      # [np.uint64[nbins+1]] * 2
         self.counters = counters    # np.int64[nbins]
@@ -130,7 +131,7 @@ def demux_batch(params, streams, last=True):
         bin_off = [np.ctypeslib.as_array(C.cast(r.bin_off[k], C.POINTER(C.c_uint64)), (nbins + 1,)).copy() for k in range(2)]
         out = [C.string_at(r.out[k], int(bin_off[k][nbins])) for k in range(2)]
         counters = np.ctypeslib.as_array(C.cast(r.counters, C.POINTER(C.c_int64)), (nbins,)).copy()
-        return OracleResult(out, bin_off, counters, int(r.n_pairs), [int(x) for x in r.consumed], [int(x) for x in r.n_skipped])
+        return OracleResult(out, bin_off, counters, int(r.n_pairs), [int(x) for x in r.consumed], [int(x) for x in r.n_skipped], bool(r.chunk_end))
     finally:
         L.qo_result_free(C.byref(r))
         del keep

@@ -224,7 +224,7 @@ int qo_demux_batch(const qo_params *p, const uint8_t *const stream[4], const uin
         for (int s = 0; s < ns && got > 0; s++) { got = next_valid(&cur[s], &rec[s]); sfail = s; }   /* Quade.py:211-214 */
         if (got < 0) { err = QO_ERR_BLANK_HEADER; goto done; }
         if (!got) {
-            if (cur[sfail].last) break;                /* StopIteration: end of chunk, Quade.py:223 */
+            if (cur[sfail].last) { res->chunk_end = 1; break; }   /* StopIteration: end of chunk, Quade.py:223 */
             /* Batch semantics (the reference has no batches): the BUFFER of file sfail ran out before its end-of-file.
              * The unfinished iteration is given back: the caller carries every tail into the next batch.  What stays
              * consumed are the invalid records in front of each file's next valid record -- the reference skips them

@@ -54,6 +54,8 @@ typedef struct {
     uint64_t n_skipped[4]; /* invalid records (len(seq)!=len(qual)) inside consumed[] (FastqReader.py:48-50) */
     int32_t nbins;
     int32_t err;
+    int32_t chunk_end;     /* the loop hit StopIteration: a file whose buffer ends at end-of-file ran dry (Quade.py:223,252) */
+    int32_t reserved;
 } qo_result;
 
 /* Demultiplex one batch of a chunk.  `last` != 0 means the buffers end at end-of-file: a final line

@@ -13,7 +13,7 @@ CTX_DEVICE_ONLY = 1
 K_NAMES = ["frame", "tilescan", "pairing", "classify", "binscan", "offsets", "compact"]
 K_COUNT = len(K_NAMES)
 SYMBOLS = ["quade_version", "quade_last_error", "quade_device_count", "quade_host_alloc", "quade_host_free",
-           "quade_ctx_create", "quade_ctx_destroy", "quade_ctx_set_samples", "quade_submit", "quade_collect",
+           "quade_ctx_create", "quade_ctx_destroy", "quade_ctx_set_samples", "quade_submit", "quade_peek", "quade_collect",
            "quade_counters", "quade_counters_reset", "quade_compute_stream"]
 
 
@@ -32,7 +32,8 @@ class Batch(C.Structure):
 class Result(C.Structure):
     _fields_ = [("ticket", C.c_uint64), ("n_pairs", C.c_uint64), ("consumed", C.c_uint64 * 4),
                 ("n_skipped", C.c_uint64 * 4), ("out", C.c_void_p * 2), ("bin_off", C.c_void_p * 2),
-                ("counters", C.c_void_p), ("nbins", C.c_int32), ("err", C.c_int32),
+                ("counters", C.c_void_p), ("nbins", C.c_int32), ("err", C.c_int32), ("chunk_end", C.c_int32),
+                ("reserved", C.c_int32),
                 ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
                 ("ms_kernel", C.c_float * K_COUNT), ("in_bytes", C.c_uint64), ("out_bytes", C.c_uint64),
                 ("gpu_launches", C.c_uint64), ("reframed_tiles", C.c_uint64)]
@@ -71,6 +72,7 @@ def lib():
     L.quade_ctx_set_samples.argtypes = [vp, vp, vp]
     L.quade_submit.argtypes = [vp, C.POINTER(Batch)]
     L.quade_collect.argtypes = [vp, C.POINTER(Result)]
+    L.quade_peek.argtypes = [vp, C.POINTER(Result)]
     L.quade_counters.argtypes = [vp, vp]
     L.quade_counters_reset.argtypes = [vp]
     L.quade_compute_stream.argtypes = [vp, C.POINTER(vp)]

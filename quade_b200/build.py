@@ -72,6 +72,27 @@ def build(force=False, verbose=False):
     return _compile_and_link(LIB, SOURCES, verbose)
 
 
+IO_LIB = os.path.join(HERE, "libquade_io.so")
+IO_DEPS = ["quade_io.cpp", os.path.join("..", "..", "include", "quade_io.h")]
+
+
+def build_io(force=False, verbose=False):
+    """Compile the host output sink (gzip-member writer pool; g++, zlib) into quade_b200/libquade_io.so."""
+    if not force and not _stale(IO_LIB, IO_DEPS):
+        return IO_LIB
+    cxx = os.environ.get("CXX") or shutil.which("g++") or "g++"
+    tmp = "%s.%d.tmp" % (IO_LIB, os.getpid())
+    cmd = [cxx, "-O2", "-g", "-std=c++17", "-fPIC", "-Wall", "-Wextra", "-shared", "-o", tmp, os.path.join(CSRC, "quade_io.cpp"),
+           "-lz", "-lpthread"]
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if verbose and out.stdout:
+        print(out.stdout)
+    if out.returncode != 0:
+        raise RuntimeError("g++ failed: %s\n%s" % (" ".join(cmd), out.stdout))
+    os.replace(tmp, IO_LIB)
+    return IO_LIB
+
+
 def build_synth(force=False, verbose=False):
     """Compile the synthetic-data generator (host + device) into quade_b200/libquade_synth.so."""
     if not force and not _stale(SYNTH_LIB, SYNTH_DEPS):
@@ -82,3 +103,4 @@ def build_synth(force=False, verbose=False):
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
     print(build_synth(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_io(force="--force" in sys.argv, verbose="-v" in sys.argv))

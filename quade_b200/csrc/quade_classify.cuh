@@ -49,6 +49,7 @@ __global__ void k_pairing(const __grid_constant__ BatchDev b)
         for (int s = 0; s < b.n_streams && first < 0; ++s)
             if (S->n_valid[s] == np) first = s;
     const bool dry = first >= 0 && ((b.last >> first) & 1);
+    S->chunk_end = dry ? 1u : 0u;
     for (int s = 0; s < b.n_streams && !S->err_capacity; ++s) {
         const StreamDev &st = b.st[s];
         const bool sq = S->n_invalid[s] != 0u;                  // vraw[v] = raw index, else v itself

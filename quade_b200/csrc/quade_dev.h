@@ -53,6 +53,7 @@ struct BatchState {
     uint32_t n_skipped[kMaxStreams];
     uint32_t err_capacity;             // some array would have overflowed
     uint32_t err_blank;                // blank header inside the parsed range
+    uint32_t chunk_end;                // a file ran dry: its buffer ends at end-of-file and holds no further valid record
     uint32_t ticket_frame;             // dynamic tile counter of k_frame
     uint32_t compact_tp;               // pairs per k_compact tile, from the mean record size (k_pairing)
     uint32_t scratch_cursor[kMaxStreams]; // k_frame: records reserved in the per-stream scratch arrays

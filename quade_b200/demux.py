@@ -14,6 +14,7 @@ class DemuxResult:
     def __init__(self, raw, nbins, device_mode):
         self.ticket = int(raw.ticket)
         self.n_pairs = int(raw.n_pairs)
+        self.chunk_end = bool(raw.chunk_end)
         self.consumed = [int(x) for x in raw.consumed]
         self.n_skipped = [int(x) for x in raw.n_skipped]
         self.nbins = nbins
@@ -143,11 +144,25 @@ class DemuxContext:
         _lib.check(self._L.quade_submit(self._ctx, C.byref(bt)))
         self._pending.append((True, keepalive))
 
+    def peek(self):
+        """The oldest batch in flight, described once its kernels are done (consumed, n_pairs, bin offsets, counters),
+        without copying its bins back and without releasing it."""
+        r = _lib.Result()
+        _lib.check(self._L.quade_peek(self._ctx, C.byref(r)))
+        return DemuxResult(r, self.nbins, True)
+
     def collect(self):
         r = _lib.Result()
         device_mode, _ = self._pending.pop(0) if self._pending else (False, None)
         _lib.check(self._L.quade_collect(self._ctx, C.byref(r)))
         return DemuxResult(r, self.nbins, device_mode)
+
+    def collect_discard(self):
+        """Release the oldest batch in flight whatever its outcome."""
+        r = _lib.Result()
+        if self._pending:
+            self._pending.pop(0)
+        self._L.quade_collect(self._ctx, C.byref(r))
 
     def run(self, streams, last=True):
         self.submit(streams, last=last)

@@ -13,6 +13,8 @@ import zlib
 from concurrent.futures import ThreadPoolExecutor
 from gzip import open as gopen
 
+import numpy as np
+
 _POOL = None
 _POOL_LOCK = threading.Lock()
 
@@ -127,3 +129,47 @@ class FastqWriter(object):
         if self._last is not None:
             self._last.result()
             self._last = None
+
+
+class BinSink(object):
+    """The batch side of the writers: one call per demultiplexed batch instead of one per record.
+
+    A batch's bins are byte ranges of the two pinned output arenas (DemuxResult.out_ptr / bin_off).  The sink creates
+    the files of every bin that receives its first record (FastqWriter.init_files: lazy creation, the reference's
+    "Create ... file" lines, src/FastqWriter.py:55-57,76-81) and hands all non-empty ranges to libquade_io.so in ONE
+    native call: gzip members are cut, compressed on all host cores and appended in order while the GPU works on the
+    next batch (src/FastqWriter.py:83-90).  No per-bin Python loop, no copy of the arena.
+    """
+
+    def __init__(self, writers, level=None, n_threads=0):
+        from ._io import GzipSink
+        self.writers = list(writers)
+        self.sink = GzipSink(n_threads, FastqWriter.COMPRESSLEVEL if level is None else level)
+        self.created = np.zeros(len(self.writers), dtype=bool)
+        self._paths = None
+
+    def begin_chunk(self):
+        """(Re)bind the bins to their files: `<name>_R?.fastq.gz`, or the chunk's `.partNNNNNN` files in a multi-GPU
+        run (FastqWriter.PART)."""
+        paths = [w._paths() for w in self.writers]
+        if paths != self._paths:
+            self.sink.set_paths([p[0] for p in paths], [p[1] for p in paths])
+            self._paths = paths
+            self.created[:] = [p[0] in w._created for w, p in zip(self.writers, paths)]
+
+    def append(self, res):
+        """res: a collected DemuxResult (host arenas).  Returns the ticket to wait on before the arenas are reused."""
+        off1, off2 = res.bin_off[0], res.bin_off[1]
+        nz = np.flatnonzero(off1[1:] > off1[:-1])
+        for b in nz[~self.created[nz]]:
+            w = self.writers[int(b)]
+            w.init_files()
+            w.counter = 0
+            self.created[b] = True
+        return self.sink.append(res.out_ptr[0] or 0, off1, res.out_ptr[1] or 0, off2, keep=res)
+
+    def wait(self, ticket):
+        self.sink.wait(ticket)
+
+    def close(self):
+        self.sink.close()

@@ -29,10 +29,13 @@ class Quade(object):
     VERSION = "Quade 0.3.2"
     USAGE = "Usage: %prog -c Conf.txt [-i -h]"
 
-    #: bytes of each file staged per batch (pinned host buffer and device slot size), env QUADE_BATCH_BYTES
+    #: new bytes of the largest file staged per batch (the other files in proportion to their record size);
+    #: env QUADE_BATCH_BYTES.  Staging buffers and device slots are sized for twice that (carry-over room).
     BATCH_BYTES = int(os.environ.get("QUADE_BATCH_BYTES", 64 << 20))
-    #: callable(quade, device) -> engine with run(streams, last) / counters(); tests inject a stand-in here
-    ENGINE_FACTORY = None
+    #: batches in flight on the device: H2D + kernels of batch N+1 beside the D2H of batch N and the gzip of N-1
+    N_SLOTS = 3
+    #: staging buffer sets: one being submitted, one being filled by the reader threads, one spare
+    N_SETS = 3
 
     @classmethod
     def class_init(cls):
@@ -109,6 +112,8 @@ class Quade(object):
             print("One of the file is incorrect or unreadable\n" + str(E))
             sys.exit(1)
         self._engine = None
+        self._stage = []
+        self._readpool = None
 
     def __str__(self):
         msg = "QUADE CLASS\n\tParameters list\n"
@@ -129,6 +134,8 @@ class Quade(object):
 
         print("Start parsing files: {} chunks to be parsed".format(len(self.seq_R1)))
         try:
+            self._open_engine()
+            Sample.SINK = self._make_sink()
             if self.idx2:
                 self.double_index_parser()
             else:
@@ -181,92 +188,170 @@ class Quade(object):
         return [(p["start"], p["end"]) for p in (self.idx1_pos, self.idx2_pos, self.mol1_pos, self.mol2_pos)]
 
     def _open_engine(self):
+        """The C-ABI context of this process's GPU (loads libquade_b200.so; raises without a CUDA device: there is
+        no CPU path).  Slots and staging buffers are sized for 2 x BATCH_BYTES: carry-over plus new bytes."""
         if self._engine is None:
-            if Quade.ENGINE_FACTORY is not None:
-                self._engine = Quade.ENGINE_FACTORY(self, self.device)
-            else:
-                from .demux import DemuxContext   # loads libquade_b200.so; raises without a CUDA device
-                self._engine = DemuxContext(self.idx2, self.spans(), self.minimal_qual,
-                                            [s.index for s in Sample.SAMPLE_LIST],
-                                            write_undetermined=Sample.WRITE_UNDETERMINED, write_pass=Sample.WRITE_PASS,
-                                            write_fail=Sample.WRITE_FAIL, device=self.device,
-                                            max_stream_bytes=self.BATCH_BYTES, n_slots=1)
+            from .demux import DemuxContext
+            self._engine = DemuxContext(self.idx2, self.spans(), self.minimal_qual,
+                                        [s.index for s in Sample.SAMPLE_LIST],
+                                        write_undetermined=Sample.WRITE_UNDETERMINED, write_pass=Sample.WRITE_PASS,
+                                        write_fail=Sample.WRITE_FAIL, device=self.device,
+                                        max_stream_bytes=2 * self.BATCH_BYTES, n_slots=self.N_SLOTS)
         return self._engine
 
+    def _make_sink(self):
+        from .fastq_writer import BinSink
+        return BinSink(Sample.BIN_WRITERS())
+
+    def _alloc_staging(self, nbytes):
+        """One page-locked staging buffer (quade_host_alloc): object with .array (numpy uint8) and .free()."""
+        from .demux import PinnedBuffer
+        return PinnedBuffer(nbytes)
+
     def _close_engine(self):
-        if self._engine is not None:
+        sink, Sample.SINK = Sample.SINK, None
+        try:
+            if sink is not None:
+                sink.close()
+        finally:
             try:
-                self._engine.close()
+                if self._engine is not None:
+                    self._engine.close()
             finally:
                 self._engine = None
-        for b in getattr(self, "_stage", []):
-            b.free()
-        self._stage = []
+                for st in getattr(self, "_stage", []):
+                    for b in st:
+                        b.free()
+                self._stage = []
+                if getattr(self, "_readpool", None) is not None:
+                    self._readpool.shutdown(wait=True)
+                    self._readpool = None
 
     def _staging(self, ns):
-        """Page-locked staging buffers, one per file of a chunk (allocated once, reused by every chunk)."""
-        if len(getattr(self, "_stage", [])) < ns:
-            if Quade.ENGINE_FACTORY is not None:
-                class _Plain:
-                    def __init__(self, n):
-                        self.array = np.empty(n, dtype=np.uint8)
-
-                    def free(self):
-                        self.array = None
-                self._stage = [_Plain(self.BATCH_BYTES) for _ in range(ns)]
-            else:
-                from .demux import PinnedBuffer
-                self._stage = [PinnedBuffer(self.BATCH_BYTES) for _ in range(ns)]
+        """N_SETS sets of page-locked staging buffers, one buffer per file of a chunk (allocated once)."""
+        if len(getattr(self, "_stage", [])) < self.N_SETS or len(self._stage[0]) < ns:
+            for st in getattr(self, "_stage", []):
+                for b in st:
+                    b.free()
+            self._stage = [[self._alloc_staging(2 * self.BATCH_BYTES) for _ in range(ns)] for _ in range(self.N_SETS)]
         return self._stage
 
     def _parse_chunk(self, n, files):
-        """The body of the reference's `while True` loop for one chunk (Quade.py:210-224 / :240-254), batched.
+        """The body of the reference's `while True` loop for one chunk (Quade.py:210-224 / :240-254), as a pipeline.
 
-        Every file is staged `BATCH_BYTES` at a time; a batch pairs as many records as all buffers hold
-        completely, the unconsumed tail of each buffer (whole records of the longer files and the trailing
-        partial line) is carried into the next batch.  The chunk ends when a file is exhausted (:223, :252).
+        A batch is, per file, the unconsumed tail of the previous batch followed by new bytes.  While batch N is on
+        the device, reader threads fill the next staging set with the new bytes of batch N+1 (placed behind room
+        for the carry-over); as soon as the kernels of batch N are done (quade_peek) its tails are copied in front
+        of them and batch N+1 is submitted; only then batch N is collected -- its D2H copy runs beside the H2D copy
+        and the kernels of N+1 -- and its bins go to the native gzip sink, which compresses and appends them on all
+        host cores while the loop goes on.  The files are read in proportion to their bytes per record, so that
+        every buffer holds about the same number of records.  The chunk ends when a file has run dry (:223, :252).
         """
-        eng = self._open_engine()
+        from concurrent.futures import ThreadPoolExecutor
+        eng = self._engine
         ns = len(files)
-        cap = self.BATCH_BYTES
+        B = self.BATCH_BYTES
+        head = B                                   # carry-over room in front of the new bytes
         if self.world > 1:
-            Sample.FLUSH_ALL()             # nothing of the previous chunk may land in this chunk's parts
+            Sample.FLUSH_ALL()                     # nothing of the previous chunk may land in this chunk's parts
             FastqWriter.PART = n
+        if Sample.SINK is not None:
+            Sample.SINK.begin_chunk()
+        if getattr(self, "_readpool", None) is None:
+            self._readpool = ThreadPoolExecutor(max_workers=4)
+        sets = [[b.array for b in st] for st in self._staging(ns)]
         readers = [FastqReader(f) for f in files]
-        bufs = [b.array for b in self._staging(ns)]
-        fill = [0] * ns
+        sink_tickets = []                          # per submitted batch: ticket of its bins in the sink (or None)
+        submitted = 0
+
+        def fill(k, want):
+            """new bytes of batch k, read by the pool into set k % N_SETS behind the carry-over room"""
+            bufs = sets[k % self.N_SETS]
+            return [self._readpool.submit(readers[s].readinto, bufs[s][head:head + want[s]]) if want[s] and not readers[s].eof
+                    else None for s in range(ns)]
+
+        def finish(res_peek):
+            """collect the oldest batch in flight and hand its bins to the writers"""
+            try:
+                res = eng.collect()
+            except RuntimeError as E:
+                if getattr(E, "code", None) == -1:              # QUADE_ERR_BLANK_HEADER
+                    # name = line.rstrip()[1:].split()[0] on a header without a token (FastqReader.py:42)
+                    raise IndexError("list index out of range") from E
+                raise
+            for s in range(ns):
+                for _ in range(int(res.n_skipped[s])):         # FastqReader.py:48-50
+                    print("Sequence length and quality string length are not equal.")
+                    print("Skipping the sequence")
+            sink_tickets.append(Sample.FINDER(res))
+
         try:
+            want = [min(B, 8 << 20)] * ns          # first batch: a probe that tells the bytes per record of every file
+            futs = fill(0, want)
+            tail = [(0, 0)] * ns                   # (offset, length) of the unconsumed bytes in the previous set
+            bpr = None
+            stalled = 0
             while True:
-                for s in range(ns):
-                    if not readers[s].eof and fill[s] < cap:
-                        fill[s] += readers[s].readinto(bufs[s][fill[s]:cap])
+                k = submitted
+                bufs = sets[k % self.N_SETS]
+                got = [f.result() if f is not None else 0 for f in futs]
                 eof = [r.eof for r in readers]
+                views = []
+                for s in range(ns):
+                    off, ln = tail[s]
+                    if ln:
+                        bufs[s][head - ln:head] = sets[(k - 1) % self.N_SETS][s][off:off + ln]
+                    views.append(bufs[s][head - ln:head + got[s]])
+                if k >= self.N_SLOTS and sink_tickets[k - self.N_SLOTS] is not None:
+                    Sample.SINK.wait(sink_tickets[k - self.N_SLOTS])   # the slot's output arenas are about to be reused
+                eng.submit(views, last=eof, ticket=k)
+                submitted += 1
+                if k >= 1:
+                    finish(None)                   # batch k-1: D2H beside the H2D and the kernels of batch k
                 try:
-                    res = eng.run([bufs[s][:fill[s]] for s in range(ns)], last=eof)
+                    res = eng.peek()               # kernels of batch k done: carry-over known
                 except RuntimeError as E:
-                    if getattr(E, "code", None) == -1:          # QUADE_ERR_BLANK_HEADER
-                        # name = line.rstrip()[1:].split()[0] on a header without a token (FastqReader.py:42)
+                    if getattr(E, "code", None) == -1:
+                        eng.collect_discard()
                         raise IndexError("list index out of range") from E
                     raise
-                for s in range(ns):
-                    for _ in range(int(res.n_skipped[s])):     # FastqReader.py:48-50
-                        print("Sequence length and quality string length are not equal.")
-                        print("Skipping the sequence")
-                Sample.FINDER(res)
+                done = res.chunk_end
+                new_tail = []
                 for s in range(ns):
                     c = int(res.consumed[s])
-                    left = fill[s] - c
-                    if c and left:
-                        bufs[s][:left] = bufs[s][c:fill[s]]      # numpy handles the overlap
-                    fill[s] = left
-                if all(eof):
+                    new_tail.append((head - tail[s][1] + c, len(views[s]) - c))
+                if not done:
+                    # bytes per record of every file -> new bytes so that all buffers hold about the same number of
+                    # records; a file that is ahead of the others reads less
+                    if res.n_pairs:
+                        bpr = [max(1.0, int(res.consumed[s]) / res.n_pairs) for s in range(ns)]
+                    progressed = res.n_pairs > 0 or any(int(c) > 0 for c in res.consumed[:ns]) or any(got)
+                    stalled = 0 if progressed else stalled + 1
+                    if bpr is None:
+                        want = [min(B, max(w, 1 << 20) * 2) for w in want]     # no complete pair yet: read more
+                    else:
+                        pairs = B / max(bpr)
+                        want = [int(min(B, max(0.0, pairs * bpr[s] - new_tail[s][1]))) & ~15 for s in range(ns)]
+                        if stalled:
+                            want = [min(B, max(w, 1 << 20) * (2 ** stalled)) for w in want]
+                    want = [min(w, 2 * B - head) for w in want]
+                    if stalled > 8 or any(t[1] > head for t in new_tail):
+                        raise IOError("a FASTQ record of chunk {} is larger than the staging buffer "
+                                      "(QUADE_BATCH_BYTES={})".format(n + 1, B))
+                    futs = fill(k + 1, want)
+                tail = new_tail
+                if done:
+                    finish(res)
                     break
-                if res.n_pairs == 0:
-                    if any(eof):
-                        break                                   # StopIteration of an exhausted file
-                    raise IOError("a FASTQ record of chunk {} is larger than the staging buffer "
-                                  "(QUADE_BATCH_BYTES={})".format(n + 1, cap))
         finally:
+            while eng.in_flight:                   # an exception above: leave no batch in flight
+                try:
+                    eng.collect()
+                except Exception:
+                    pass
+            for t in sink_tickets:
+                if t is not None and Sample.SINK is not None:
+                    Sample.SINK.wait(t)
             for r in readers:
                 r.close()
 

@@ -40,6 +40,7 @@ class Sample(object):
         cls.SAMPLE_LIST = []
         cls.MIN_QUAL = 0
         cls.UNDETERMINED_WRITER = FastqWriter(name="Undetermined")
+        cls.SINK = None
 
     @classmethod
     def BIN_WRITERS(cls):
@@ -81,24 +82,32 @@ class Sample(object):
             c += [s.pass_qual, s.fail_qual]
         return c
 
+    #: BinSink of the running Quade (native gzip-member writer pool); None: FINDER writes through the FastqWriters
+    SINK = None
+
     @classmethod
     def FINDER(cls, batch, *per_record_args):
         """Apply one demultiplexed batch (Sample.py:56-91, batched).
 
         `batch` is a DemuxResult: the GPU already looked every fused index up, checked min phred against MIN_QUAL
-        and serialised the records per bin.  The reference's per-record form FINDER(read1, read2, index,
-        molecular) has no CPU implementation here.
+        and serialised the records per bin.  The counters move by the per-bin pair counts; every non-empty bin range
+        goes to its files -- through the native sink (one call per batch; returns its ticket) when a Quade run has
+        installed one, else through the bins' FastqWriter objects.  The reference's per-record form
+        FINDER(read1, read2, index, molecular) has no CPU implementation here.
         """
-        if per_record_args or not hasattr(batch, "bin_view"):
+        if per_record_args or not hasattr(batch, "bin_off"):
             raise TypeError("Sample.FINDER takes one DemuxResult per batch; the per-record CPU form of the "
                             "reference (Sample.py:57) is replaced by the CUDA path and is not provided")
         cls.ADD_COUNTS(batch.counters)
+        if cls.SINK is not None:
+            return cls.SINK.append(batch)
         writers = cls.BIN_WRITERS()
         for b, w in enumerate(writers):
             r1 = batch.bin_view(0, b)
             if len(r1) == 0:
                 continue                      # write flag off (Sample.py:74,82,90) or no pair in this bin
             w(r1, batch.bin_view(1, b), n_records=int(batch.counters[b]))
+        return None
 
     @classmethod
     def FLUSH_ALL(cls):

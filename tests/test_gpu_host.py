@@ -17,7 +17,6 @@ def test_golden_run_on_the_gpu(tmp_path, monkeypatch, batch_bytes):
     _fresh()
     wd = _stage_dataset(tmp_path)
     monkeypatch.chdir(wd)
-    monkeypatch.setattr(Quade, "ENGINE_FACTORY", None)
     monkeypatch.setattr(Quade, "BATCH_BYTES", batch_bytes)
     q = Quade(conf_file="Quade_conf_file.txt")
     assert q() == 0
@@ -46,3 +45,59 @@ def test_sharded_run_two_gpus_nccl(tmp_path):
                           "Quade_conf_file.txt"], cwd=str(wd), env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout + out.stderr
     _check_golden_outputs(wd)
+
+
+@pytest.mark.parametrize("gz_in,level", [(False, 1), (True, 0)])
+def test_overlapped_pipeline_three_chunks_many_batches_matches_oracle(tmp_path, monkeypatch, gz_in, level):
+    """The whole tool through the overlapped path: 3 chunks of 60 k synthetic cfg3 pairs as files (plain or gzip),
+    staged 4 MiB at a time (>= 5 batches per chunk, three in flight: reader threads, H2D + kernels, D2H, native gzip
+    sink), 769 bins.  EVERY output file is compared, decompressed, with the oracle's per-bin streams over the chunks in
+    order; so are the file set (lazy creation) and the report counters."""
+    import gzip
+    import numpy as np
+    from oracle import oracle as O
+    from quade_b200.fastq_writer import FastqWriter
+    from quade_b200.quade import Quade
+    from quade_b200.sample import Sample
+    from quade_b200.synth import Synth
+    _fresh()
+    s = Synth.from_config("cfg3")
+    per, chunks = 60_000, 3
+    wd = tmp_path / "run"
+    wd.mkdir()
+    monkeypatch.chdir(wd)
+    names = [[] for _ in range(4)]
+    p = O.OracleParams(s.dual, s.spans(), s.min_qual, s.sample_keys())
+    acc = [[bytearray(), bytearray()] for _ in range(p.nbins)]
+    counters = np.zeros(p.nbins, dtype=np.int64)
+    for c in range(chunks):
+        arrays = s.generate(c * per, per)
+        for k, a in enumerate(arrays):
+            fn = "C%d_%d.fastq%s" % (c, k, ".gz" if gz_in else "")
+            if gz_in:
+                with gzip.open(fn, "wb", compresslevel=1) as fh:
+                    fh.write(memoryview(a))
+            else:
+                a.tofile(fn)
+            names[k].append(fn)
+        ref = O.demux_batch(p, arrays, last=True)
+        counters += ref.counters
+        for b in range(p.nbins):
+            acc[b][0] += ref.bin_bytes(0, b)
+            acc[b][1] += ref.bin_bytes(1, b)
+    with open("conf.txt", "w") as fh:
+        fh.write(s.conf_text(names))
+    monkeypatch.setattr(Quade, "BATCH_BYTES", 4 << 20)
+    monkeypatch.setattr(FastqWriter, "COMPRESSLEVEL", level)
+    assert Quade(conf_file="conf.txt")() == 0
+    assert Sample.COUNTS() == [int(x) for x in counters]
+    bins = O.bin_names(s.sample_names())
+    expect = {}
+    for n, (a, b) in zip(bins, acc):
+        if len(a) or len(b):
+            expect[n + "_R1.fastq.gz"], expect[n + "_R2.fastq.gz"] = bytes(a), bytes(b)
+    got = sorted(f for f in os.listdir(".") if f.endswith(".fastq.gz") and not f.startswith("C"))
+    assert got == sorted(expect)
+    for f in got:
+        with gzip.open(f, "rb") as fh:
+            assert fh.read() == expect[f], f

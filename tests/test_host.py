@@ -71,7 +71,7 @@ def test_golden_run_through_the_host_loop(tmp_path, monkeypatch, batch_bytes):
     _fresh()
     wd = _stage_dataset(tmp_path)
     monkeypatch.chdir(wd)
-    monkeypatch.setattr(Quade, "ENGINE_FACTORY", util.OracleEngine)
+    util.patch_host_engine(Quade, monkeypatch)
     monkeypatch.setattr(Quade, "BATCH_BYTES", batch_bytes)
     q = Quade(conf_file="Quade_conf_file.txt")
     assert q() == 0
@@ -93,7 +93,7 @@ def test_golden_run_with_plain_text_inputs(tmp_path, monkeypatch, batch_bytes):
     conf = (wd / "Quade_conf_file.txt").read_text().replace(".fastq.gz", ".fastq")
     (wd / "Quade_conf_file.txt").write_text(conf)
     monkeypatch.chdir(wd)
-    monkeypatch.setattr(Quade, "ENGINE_FACTORY", util.OracleEngine)
+    util.patch_host_engine(Quade, monkeypatch)
     monkeypatch.setattr(Quade, "BATCH_BYTES", batch_bytes)
     q = Quade(conf_file="Quade_conf_file.txt")
     assert all(f.endswith(".fastq") for f in q.seq_R1 + q.seq_R2 + q.index_R1 + q.index_R2)
@@ -173,7 +173,7 @@ def test_sharded_run_world_size_2_gloo(tmp_path):
         "import sys; sys.path.insert(0, %r)\n"
         "from tests import util\n"
         "from quade_b200.quade import Quade\n"
-        "Quade.ENGINE_FACTORY = util.OracleEngine\n"
+        "util.patch_host_engine(Quade)\n"
         "Quade.BATCH_BYTES = 4096\n"
         "sys.exit(Quade(conf_file='Quade_conf_file.txt')())\n" % ROOT)
     procs = []
@@ -186,3 +186,41 @@ def test_sharded_run_world_size_2_gloo(tmp_path):
     assert [p.returncode for p in procs] == [0, 0], outs
     _check_golden_outputs(wd)
     assert "Start parsing chunk 2" in outs[1] and "Start parsing chunk 2" not in outs[0]
+
+
+def test_native_gzip_sink_keeps_member_order_and_handles_stored_blocks(tmp_path):
+    """libquade_io.so: members of one file are appended in submission order whatever thread compressed them; level 0
+    writes stored blocks (valid gzip); empty bins produce nothing; the arenas are released by wait()."""
+    import numpy as np
+    from quade_b200._io import GzipSink
+    rng = np.random.default_rng(5)
+    nb = 7
+    r1 = [str(tmp_path / ("b%d_R1.fastq.gz" % b)) for b in range(nb)]
+    r2 = [str(tmp_path / ("b%d_R2.fastq.gz" % b)) for b in range(nb)]
+    for level in (0, 1):
+        for p in r1 + r2:
+            gzip.open(p, "wb").close()                       # lazy creation is the caller's job
+        sink = GzipSink(n_threads=5, level=level)
+        sink.set_paths(r1, r2)
+        expect = [[bytearray(), bytearray()] for _ in range(nb)]
+        tickets = []
+        for batch in range(12):
+            arenas, offs = [], []
+            for k in range(2):
+                sizes = rng.integers(0, 3000, nb) * (rng.random(nb) < 0.7)
+                off = np.zeros(nb + 1, dtype=np.uint64)
+                np.cumsum(sizes, out=off[1:])
+                a = rng.integers(65, 91, int(off[-1]) + 1, dtype=np.uint8)
+                for b in range(nb):
+                    expect[b][k] += a[int(off[b]):int(off[b + 1])].tobytes()
+                arenas.append(a)
+                offs.append(off)
+            tickets.append(sink.append(arenas[0].ctypes.data, offs[0], arenas[1].ctypes.data, offs[1], keep=arenas))
+        sink.wait(tickets[-1])
+        n_in, n_out = sink.stats()
+        assert n_in == sum(len(e[0]) + len(e[1]) for e in expect) and n_out > 0
+        sink.close()
+        for b in range(nb):
+            for k, paths in enumerate((r1, r2)):
+                with gzip.open(paths[b], "rb") as fh:
+                    assert fh.read() == bytes(expect[b][k]), (level, b, k)

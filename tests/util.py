@@ -96,13 +96,18 @@ def quade_dataset():
 
 
 class OracleEngine:
-    """Stand-in for DemuxContext in CPU-only tests of the HOST logic (batching, carry-over, writers, sharding):
-    same run()/close() surface, answers computed by the oracle.  Test infrastructure only."""
+    """Stand-in for DemuxContext in CPU-only tests of the HOST logic (pipeline, carry-over, writers, sharding):
+    the same submit / peek / collect surface, answers computed by the oracle.  Test infrastructure only: installed
+    by monkeypatching Quade._open_engine / Quade._alloc_staging (see patch_host_engine)."""
 
     class _Res:
-        def __init__(self, r):
-            self.n_pairs, self.consumed, self.n_skipped = r.n_pairs, list(r.consumed), list(r.n_skipped)
-            self.counters, self._r = r.counters, r
+        def __init__(self, r, ticket):
+            self.ticket = ticket
+            self.n_pairs, self.consumed, self.n_skipped = r.n_pairs, list(r.consumed) + [0] * (4 - len(r.consumed)), list(r.n_skipped) + [0] * (4 - len(r.n_skipped))
+            self.chunk_end = r.chunk_end
+            self.counters, self.bin_off, self._r = r.counters, r.bin_off, r
+            self._arena = [np.frombuffer(r.out[k], dtype=np.uint8) if len(r.out[k]) else np.zeros(1, dtype=np.uint8) for k in range(2)]
+            self.out_ptr = [a.ctypes.data for a in self._arena]
 
         def bin_view(self, read, b):
             return memoryview(self._r.bin_bytes(read, b))
@@ -112,15 +117,66 @@ class OracleEngine:
         self.params = O.OracleParams(quade.idx2, quade.spans(), quade.minimal_qual, [s.index for s in Sample.SAMPLE_LIST],
                                      Sample.WRITE_UNDETERMINED, Sample.WRITE_PASS, Sample.WRITE_FAIL)
         self.batches = 0
+        self._q = []
 
-    def run(self, streams, last=True):
+    @property
+    def in_flight(self):
+        return len(self._q)
+
+    def submit(self, streams, last=True, ticket=0):
         self.batches += 1
         try:
-            return self._Res(O.demux_batch(self.params, [bytes(s) for s in streams], last=list(last) if isinstance(last, (list, tuple)) else last))
+            r = O.demux_batch(self.params, [bytes(s) for s in streams], last=list(last) if isinstance(last, (list, tuple)) else last)
+            self._q.append(self._Res(r, ticket))
         except O.OracleError as e:
             err = RuntimeError("oracle error %d" % e.code)
             err.code = e.code
-            raise err
+            self._q.append(err)
+
+    def peek(self):
+        if isinstance(self._q[0], Exception):
+            raise self._q[0]
+        return self._q[0]
+
+    def collect(self):
+        r = self._q.pop(0)
+        if isinstance(r, Exception):
+            raise r
+        return r
+
+    def collect_discard(self):
+        if self._q:
+            self._q.pop(0)
+
+    def run(self, streams, last=True):
+        self.submit(streams, last)
+        return self.collect()
 
     def close(self):
         pass
+
+
+class _PlainBuffer:
+    def __init__(self, n):
+        self.array = np.empty(n, dtype=np.uint8)
+
+    def free(self):
+        self.array = None
+
+
+def patch_host_engine(Quade, monkeypatch=None):
+    """Replace the device of Quade by the oracle (and the pinned staging memory by numpy arrays) for CPU-only tests of
+    the host pipeline.  The product class has no switch for this: the methods are patched from here."""
+    def _open_engine(self):
+        if self._engine is None:
+            self._engine = OracleEngine(self, self.device)
+        return self._engine
+
+    def _alloc_staging(self, nbytes):
+        return _PlainBuffer(nbytes)
+    if monkeypatch is not None:
+        monkeypatch.setattr(Quade, "_open_engine", _open_engine)
+        monkeypatch.setattr(Quade, "_alloc_staging", _alloc_staging)
+    else:
+        Quade._open_engine = _open_engine
+        Quade._alloc_staging = _alloc_staging
