@@ -46,6 +46,7 @@ def parse_args():
     ap.add_argument("--distinct", type=int, default=0,
                     help="distinct device-generated chunks the steps cycle through (0 = one per step incl. warm-up, capped by --distinct-gb)")
     ap.add_argument("--distinct-gb", type=float, default=48.0, help="HBM budget for the resident input chunks")
+    ap.add_argument("--no-bind", action="store_true", help="do not bind the rank's threads and pinned pages next to its GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--slots", type=int, default=6,
@@ -278,6 +279,8 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     sampler = ClockSampler(local_rank)                 # forked now, while this process is still small
+    from quade_b200 import affinity
+    placement = affinity.bind_to_gpu(local_rank, world) if not args.no_bind else {"mode": "off"}   # before any pinned allocation
     synth = Synth.from_config(args.config)
     min_qual = synth.min_qual if args.min_qual is None else args.min_qual
     P, ns = args.pairs, synth.n_streams
@@ -426,7 +429,8 @@ def run_ours(args, rank, world, local_rank):
         e2e = {"value": world * P * args.steps / float(tt.item()), "unit": UNIT,
                "h2d_bytes_per_step": int(sum(sizes0)), "d2h_bytes_per_step": int(e_out[0]),
                "timing": "wall clock between device synchronisations, max over ranks",
-               "pcie_GBps_per_gpu": (sum(sizes0) + e_out[0]) * args.steps / float(tt.item()) / 1e9}
+               "pcie_GBps_per_gpu": (sum(sizes0) + e_out[0]) * args.steps / float(tt.item()) / 1e9,
+               "placement": placement}
         ectx.close()
 
     # ---- CPU baseline: rank 0, N=1 only: the reference's own Python on one core; the C port on all cores beside it --

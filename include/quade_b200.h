@@ -14,7 +14,8 @@
  *                              + Sample.FINDER                                        src/Sample.py:56-91
  *                              + FastqWriter.__call__ / FastqSeq.fastqstr             src/FastqWriter.py:48-74,
  *                                                                                     src/pyFastq/FastqSeq.py:68-82
- *   quade_counters          <- Sample.TOTAL/PASS_QUAL/FAIL_QUAL/UNDETERMINED and
+ *   quade_counters, quade_allreduce_counters
+ *                           <- Sample.TOTAL/PASS_QUAL/FAIL_QUAL/UNDETERMINED and
  *                              per-sample pass_qual/fail_qual                         src/Sample.py:32,144
  *
  * Plain C, no exceptions cross the boundary.  Every call returns 0 (QUADE_OK) or a negative quade_err;
@@ -145,6 +146,12 @@ int quade_collect(quade_ctx *ctx, quade_result *res);
 /* cumulative pair counts since ctx creation / reset: int64[1+2*n_samples] in bin order */
 int quade_counters(quade_ctx *ctx, int64_t *out);
 int quade_counters_reset(quade_ctx *ctx);
+/* The path's only collective (src/Sample.py:32,144: the counters are class-level sums): replaces the cumulative
+ * counters of each of the n contexts -- one per GPU of this process, no batch in flight -- by their sum over all of
+ * them (single-process ncclCommInitAll + one ncclAllReduce(int64, sum) of 1+2*n_samples values per GPU; NCCL is
+ * loaded at run time, QUADE_ERR_UNSUPPORTED if libnccl.so.2 cannot be found).  Multi-process callers (one rank per
+ * GPU) reduce quade_counters() with their own communicator instead (quade_b200/parallel.py). */
+int quade_allreduce_counters(quade_ctx *const *ctxs, int n);
 /* CUDA stream handle (cudaStream_t) kernels are launched on, for callers that time with their own events */
 int quade_compute_stream(quade_ctx *ctx, void **stream);
 

@@ -56,7 +56,7 @@ def _compile_and_link(lib, sources, verbose):
             if p.returncode != 0:
                 raise RuntimeError("nvcc failed: %s\n%s" % (" ".join(cmd), out))
         tmp = "%s.%d.tmp" % (lib, os.getpid())
-        subprocess.check_call([nvcc, "-shared", "-cudart", "static", "-Wno-deprecated-gpu-targets", "-o", tmp] + objs + ["-lpthread"])
+        subprocess.check_call([nvcc, "-shared", "-cudart", "static", "-Wno-deprecated-gpu-targets", "-o", tmp] + objs + ["-lpthread", "-ldl"])
         os.replace(tmp, lib)
     finally:
         for o in objs:

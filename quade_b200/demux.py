@@ -203,3 +203,10 @@ class PinnedBuffer:
             self.free()
         except Exception:
             pass
+
+
+def allreduce_counters(contexts):
+    """Sum the cumulative counters of several DemuxContext objects (one per GPU of this process) in place:
+    quade_allreduce_counters, NCCL over NVLink."""
+    arr = (C.c_void_p * len(contexts))(*[c._ctx for c in contexts])
+    _lib.check(_lib.lib().quade_allreduce_counters(arr, len(contexts)))

@@ -36,6 +36,9 @@ class Quade(object):
     N_SLOTS = 3
     #: staging buffer sets: one being submitted, one being filled by the reader threads, one spare
     N_SETS = 3
+    #: chunks whose files are opened ahead of the one being parsed: a gzip file is inflated by its own thread, so the
+    #: files of the next chunks inflate on idle cores while this chunk is on the device (FastqReader.py:30)
+    CHUNKS_AHEAD = 2
 
     @classmethod
     def class_init(cls):
@@ -114,6 +117,8 @@ class Quade(object):
         self._engine = None
         self._stage = []
         self._readpool = None
+        import collections
+        self._prof = collections.defaultdict(float)
 
     def __str__(self):
         msg = "QUADE CLASS\n\tParameters list\n"
@@ -129,20 +134,27 @@ class Quade(object):
     def __call__(self):
         """Main function of the script (Quade.py:169-193)"""
         start_time = time()
-        self.rank, self.world, _ = parallel.init_process_group()
+        self.rank, self.world, local_rank = parallel.init_process_group()
         FastqWriter.PART = None
+        if self.world > 1 and not os.environ.get("QUADE_NO_BIND"):
+            from . import affinity
+            affinity.bind_to_gpu(local_rank, self.world)      # threads and pinned pages of this rank next to its GPU
 
         print("Start parsing files: {} chunks to be parsed".format(len(self.seq_R1)))
         try:
+            t0 = time()
             self._open_engine()
             Sample.SINK = self._make_sink()
+            self._prof["open engine + sink"] += time() - t0
             if self.idx2:
                 self.double_index_parser()
             else:
                 self.simple_index_parser()
             Sample.FLUSH_ALL()
         finally:
+            t0 = time()
             self._close_engine()
+            self._prof["close"] += time() - t0
 
         if self.world > 1:
             # the path's only collective: the report counters; then restore bin order by chunk index
@@ -162,23 +174,30 @@ class Quade(object):
                 for descr, value in Sample.REPORT():
                     report.write("{}\t{}\n".format(descr, value))
 
+        if os.environ.get("QUADE_PROFILE"):
+            print("profile (s): " + ", ".join("{} {:.3f}".format(k, v) for k, v in sorted(self._prof.items())))
         print("Done in {}s".format(round(time() - start_time, 3)))
         return 0
 
     def double_index_parser(self):
         """Quade.py:195-224: chunk n = n-th file of seq_R1, seq_R2, index_R1, index_R2"""
         chunks = list(zip(self.seq_R1, self.seq_R2, self.index_R1, self.index_R2))
-        for n in parallel.chunks_of_rank(len(chunks), self.rank, self.world):
+        mine = parallel.chunks_of_rank(len(chunks), self.rank, self.world)
+        for i, n in enumerate(mine):
             print("Start parsing chunk {}".format(n + 1))
+            self._open_ahead(chunks, mine[i:i + 1 + self.CHUNKS_AHEAD])
             self._parse_chunk(n, chunks[n])
             print("\tEnd of chunk {}".format(n + 1))
 
     def simple_index_parser(self):
         """Quade.py:226-254"""
         chunks = list(zip(self.seq_R1, self.seq_R2, self.index_R1))
-        for n in parallel.chunks_of_rank(len(chunks), self.rank, self.world):
+        mine = parallel.chunks_of_rank(len(chunks), self.rank, self.world)
+        for i, n in enumerate(mine):
             print("Start parsing chunk {}/{}".format(n + 1, len(self.seq_R1)))
+            self._open_ahead(chunks, mine[i:i + 1 + self.CHUNKS_AHEAD])
             self._parse_chunk(n, chunks[n])
+            print("\t{} sequences parsed".format(self._chunk_pairs))     # the reader's line, FastqReader.py:57-58
             print("\tEnd of chunk {}".format(n + 1))
 
     # ~~~~~~~PRIVATE METHODS~~~~~~~#
@@ -198,6 +217,14 @@ class Quade(object):
                                         write_fail=Sample.WRITE_FAIL, device=self.device,
                                         max_stream_bytes=2 * self.BATCH_BYTES, n_slots=self.N_SLOTS)
         return self._engine
+
+    def _open_ahead(self, chunks, which):
+        """FastqReader objects of the chunks in `which` (the current one first), opened now."""
+        if not hasattr(self, "_opened"):
+            self._opened = {}
+        for n in which:
+            if n not in self._opened:
+                self._opened[n] = [FastqReader(f, depth=16 if n != which[0] else 4) for f in chunks[n]]
 
     def _make_sink(self):
         from .fastq_writer import BinSink
@@ -223,6 +250,10 @@ class Quade(object):
                     for b in st:
                         b.free()
                 self._stage = []
+                for rs in getattr(self, "_opened", {}).values():
+                    for r in rs:
+                        r.close()
+                self._opened = {}
                 if getattr(self, "_readpool", None) is not None:
                     self._readpool.shutdown(wait=True)
                     self._readpool = None
@@ -260,9 +291,12 @@ class Quade(object):
         if getattr(self, "_readpool", None) is None:
             self._readpool = ThreadPoolExecutor(max_workers=4)
         sets = [[b.array for b in st] for st in self._staging(ns)]
-        readers = [FastqReader(f) for f in files]
+        readers = getattr(self, "_opened", {}).pop(n, None) or [FastqReader(f) for f in files]
+        self._chunk_pairs = 0
         sink_tickets = []                          # per submitted batch: ticket of its bins in the sink (or None)
         submitted = 0
+        prof = self._prof                          # seconds per pipeline stage (QUADE_PROFILE=1 prints them)
+        clock = time
 
         def fill(k, want):
             """new bytes of batch k, read by the pool into set k % N_SETS behind the carry-over room"""
@@ -294,20 +328,31 @@ class Quade(object):
             while True:
                 k = submitted
                 bufs = sets[k % self.N_SETS]
+                t0 = clock()
                 got = [f.result() if f is not None else 0 for f in futs]
+                prof["wait readers"] += clock() - t0
                 eof = [r.eof for r in readers]
+                t0 = clock()
                 views = []
                 for s in range(ns):
                     off, ln = tail[s]
                     if ln:
                         bufs[s][head - ln:head] = sets[(k - 1) % self.N_SETS][s][off:off + ln]
                     views.append(bufs[s][head - ln:head + got[s]])
+                prof["carry-over copy"] += clock() - t0
+                t0 = clock()
                 if k >= self.N_SLOTS and sink_tickets[k - self.N_SLOTS] is not None:
                     Sample.SINK.wait(sink_tickets[k - self.N_SLOTS])   # the slot's output arenas are about to be reused
+                prof["wait sink"] += clock() - t0
+                t0 = clock()
                 eng.submit(views, last=eof, ticket=k)
                 submitted += 1
+                prof["submit"] += clock() - t0
+                t0 = clock()
                 if k >= 1:
                     finish(None)                   # batch k-1: D2H beside the H2D and the kernels of batch k
+                prof["collect + sink append"] += clock() - t0
+                t0 = clock()
                 try:
                     res = eng.peek()               # kernels of batch k done: carry-over known
                 except RuntimeError as E:
@@ -315,6 +360,9 @@ class Quade(object):
                         eng.collect_discard()
                         raise IndexError("list index out of range") from E
                     raise
+                prof["peek"] += clock() - t0
+                prof["batches"] += 1
+                self._chunk_pairs += res.n_pairs
                 done = res.chunk_end
                 new_tail = []
                 for s in range(ns):

@@ -387,3 +387,28 @@ def test_sampled_chunks_of_the_scale_config_match_the_oracle_by_checksum():
             assert (r.bin_off[k] == ref.bin_off[k]).all()
             assert _bin_checksums(r.arena(k), r.bin_off[k]) == _bin_checksums(np.frombuffer(ref.out[k], dtype=np.uint8), ref.bin_off[k])
     ctx.close()
+
+
+def test_allreduce_counters_c_abi():
+    """quade_allreduce_counters: the single-process form of the path's only collective (one context per GPU, NCCL).
+    With one GPU it is the identity and refuses two contexts on one device; with two it sums."""
+    import torch
+    from quade_b200 import DemuxContext, QuadeError
+    from quade_b200.demux import allreduce_counters
+    good = b"@a\nACGT\n+\nIIII\n"
+    spans = [(0, 4), (0, 0), (0, 0), (0, 0)]
+    n_dev = torch.cuda.device_count()
+    ctxs = [DemuxContext(False, spans, 0, ["ACGT", "TTTT"], device=d % n_dev, max_stream_bytes=1 << 16, max_pairs=64) for d in range(2)]
+    ctxs[0].run([good * 3, good * 3, good * 3])
+    ctxs[1].run([good * 5, good * 5, good.replace(b"ACGT", b"GGGG") * 5])
+    allreduce_counters(ctxs[:1])
+    assert list(ctxs[0].counters()) == [0, 3, 0, 0, 0]
+    if n_dev < 2:
+        with pytest.raises(QuadeError) as e:
+            allreduce_counters(ctxs)
+        assert e.value.code == -5                     # two contexts on one device
+    else:
+        allreduce_counters(ctxs)
+        assert list(ctxs[0].counters()) == list(ctxs[1].counters()) == [5, 3, 0, 0, 0]
+    for c in ctxs:
+        c.close()

@@ -15,10 +15,16 @@ os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
 os.environ.setdefault("MASTER_PORT", "29533")
 dist.init_process_group("gloo", rank=rank, world_size=world)
 torch.cuda.set_device(local)
-if os.environ.get("PROBE_AFFINITY"):            # pin the rank (and its first-touch pinned pages) to a CPU slice
-    cpus = sorted(os.sched_getaffinity(0))
-    per = max(1, len(cpus) // world)
-    os.sched_setaffinity(0, cpus[local * per:(local + 1) * per] or cpus)
+import sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from quade_b200 import affinity  # noqa: E402
+loc = affinity.gpu_locality(local)
+if os.environ.get("PROBE_AFFINITY"):            # pin the rank (and its first-touch pinned pages) next to its GPU
+    loc = affinity.bind_to_gpu(local, world)
+infos = [None] * world
+dist.all_gather_object(infos, {k: v for k, v in loc.items() if k != "local_cpus"})
+if rank == 0:
+    print("binding:", "on" if os.environ.get("PROBE_AFFINITY") else "off", infos, flush=True)
 n = 1 << 30
 h_in = torch.empty(n, dtype=torch.uint8).pin_memory()
 h_out = torch.empty(n, dtype=torch.uint8).pin_memory()
