@@ -38,7 +38,9 @@ class Quade(object):
     N_SETS = 3
     #: chunks whose files are opened ahead of the one being parsed: a gzip file is inflated by its own thread, so the
     #: files of the next chunks inflate on idle cores while this chunk is on the device (FastqReader.py:30)
-    CHUNKS_AHEAD = 2
+    CHUNKS_AHEAD = 3
+    #: decompressed bytes a file opened ahead may hold ready (8 MiB blocks): 3 chunks x 4 files x 384 MiB at most
+    AHEAD_BLOCKS = 48
 
     @classmethod
     def class_init(cls):
@@ -224,7 +226,7 @@ class Quade(object):
             self._opened = {}
         for n in which:
             if n not in self._opened:
-                self._opened[n] = [FastqReader(f, depth=16 if n != which[0] else 4) for f in chunks[n]]
+                self._opened[n] = [FastqReader(f, depth=self.AHEAD_BLOCKS if n != which[0] else 4) for f in chunks[n]]
 
     def _make_sink(self):
         from .fastq_writer import BinSink
