@@ -10,11 +10,15 @@ static int g_f_ctas = 0, g_c_ctas = 0;      // CTAs per SM when k_frame and k_co
 
 static void init_launch_config()
 {
-    if (g_sms) return;
-    if (const char *v = getenv("QUADE_F_CTAS")) g_f_ctas = atoi(v);
-    if (const char *v = getenv("QUADE_C_CTAS")) g_c_ctas = atoi(v);
+    // function attributes (dynamic shared memory above 48 KiB) are per DEVICE: a process that drives several GPUs
+    // (quade_allreduce_counters: one context per GPU) sets them on each device it launches on
+    static unsigned long long done_mask = 0ull;
     int dev = 0;
     cudaGetDevice(&dev);
+    if (dev < 64 && (done_mask >> dev) & 1ull) return;
+    if (dev < 64) done_mask |= 1ull << dev;
+    if (const char *v = getenv("QUADE_F_CTAS")) g_f_ctas = atoi(v);
+    if (const char *v = getenv("QUADE_C_CTAS")) g_c_ctas = atoi(v);
     cudaDeviceGetAttribute(&g_sms, cudaDevAttrMultiProcessorCount, dev);
     cudaFuncSetAttribute(k_frame<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM_FAST);
     cudaFuncSetAttribute(k_frame<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FT_SMEM_REDO);
