@@ -299,6 +299,13 @@ extern "C" int quade_ctx_destroy(quade_ctx *c)
     if (!c) return QUADE_OK;
     cudaSetDevice(c->device);
     cudaDeviceSynchronize();
+#if QUADE_CHECKS
+    {
+        unsigned int t[2];
+        debug_check_tally(t);
+        fprintf(stderr, "QUADE_CHECKS: %u violations (first code %u)\n", t[0], t[1]);
+    }
+#endif
     for (auto &sl : c->slots) slot_free(sl);
     if (c->d_entries) cudaFree(c->d_entries);
     if (c->d_disp) cudaFree(c->d_disp);

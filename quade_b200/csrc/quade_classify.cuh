@@ -130,6 +130,7 @@ __global__ void __launch_bounds__(C2T) k_classify(const __grid_constant__ BatchD
         }
         for (; p < end; p += C2T) {
             const uint32_t v1 = nv1, v2 = nv2, r1 = nr1, r2 = nr2;
+            QCHK(v1 < i1.cap_rec && (!b.dual || v2 < i2.cap_rec) && r1 < b.st[0].cap_rec && r2 < b.st[1].cap_rec && p < b.cap_pairs, 301u);
             if (p + C2T < end) {
                 nv1 = i1.loc[p + C2T];
                 nv2 = b.dual ? i2.loc[p + C2T] : 0u;

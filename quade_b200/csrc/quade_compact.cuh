@@ -77,6 +77,7 @@ __device__ __forceinline__ void emit_generic(const BatchDev &b, int k, uint32_t 
         else if (x < D2) ch = (x - D1 - L == 1u) ? '+' : '\n';
         else if (x < D2 + L) ch = data[rc.z + x - D2];
         else ch = '\n';
+        QCHK((size_t)ooff + x < b.state->out_total[k], 206u);
         gout[x] = (uint8_t)ch;
     }
 }
@@ -211,6 +212,8 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
     };
     auto issue = [&](const TileMeta &m, uint32_t stage) {
         if (lane == 0 && (m.size0 | m.size1)) {
+            QCHK(m.size0 <= (uint32_t)C3_CAP && m.size1 <= (uint32_t)C3_CAP && (m.size0 & 15u) == 0u && (m.size1 & 15u) == 0u &&
+                     (m.start0 & 15u) == 0u && (m.start1 & 15u) == 0u, 205u);
             const uint32_t bar = s_bar + 8u * stage;
             fence_proxy_async();
             mbar_expect_tx(bar, m.size0 + m.size1);
@@ -313,6 +316,8 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
                 const uint32_t v = lane, y0 = 16u * v;
                 const uint32_t sa = ((y0 < hend ? hbi : sb) + y0) & ~15u;
                 const uint4 val = shift_bytes_sel(lds128(sa), lds128(sa + 16u), sr);
+                QCHK(!(v >= vlo && v < F1) || (sa >= s_in && sa + 32u <= s_bar), 201u);
+                QCHK(!(v >= vlo && v < F1) || (gdst + y0 >= b.out[i >= tp ? 1 : 0] && gdst + y0 + 16u <= b.out[i >= tp ? 1 : 0] + St->out_total[i >= tp ? 1 : 0]), 202u);
                 if (v >= vlo && v < F1) *reinterpret_cast<uint4 *>(gdst + y0) = val;
             }
             if (F1 > 32u) {                                                        // records longer than 512 bytes
@@ -326,6 +331,8 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
             const uint32_t y = lane < 16 ? (uint32_t)lane : 16u * F1 + (uint32_t)(lane - 16);
             const bool okb = lane < 16 ? (y >= h0 && y < h1) : y < t1;
             const uint32_t bsrc = (y < hend ? hbi : sb) + y;
+            QCHK(!okb || (bsrc >= s_in && bsrc < s_bar), 203u);
+            QCHK(!okb || (gdst + y >= b.out[i >= tp ? 1 : 0] && gdst + y < b.out[i >= tp ? 1 : 0] + St->out_total[i >= tp ? 1 : 0]), 204u);
             if (okb) gdst[y] = (uint8_t)lds8(bsrc);
         }
         if (slow) {                                                                // records off the fast path

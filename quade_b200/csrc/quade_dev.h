@@ -137,6 +137,7 @@ void launch_binscan(const BatchDev &b, cudaStream_t s);    // k_binscan_blocks, 
 void launch_offsets(const BatchDev &b, cudaStream_t s);
 void launch_compact(const BatchDev &b, cudaStream_t s);
 size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
+void debug_check_tally(unsigned int out[2]);   // QUADE_CHECKS builds: {violations, first code}
 
 #ifndef QUADE_F_TILE
 #define QUADE_F_TILE 32768

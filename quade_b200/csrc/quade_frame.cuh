@@ -228,6 +228,13 @@ __device__ __noinline__ uint4 g_digest(const BatchDev &b, const StreamDev &st, i
 // 64 mask bits of the bytes <= 0x20 among the 64 bytes at the 16-byte aligned shared address a
 __device__ __forceinline__ u64 f_cand64(uint32_t a)
 {
+#if QUADE_CHECKS
+    {
+        extern __shared__ __align__(128) uint8_t f_smem_chk[];
+        const uint32_t lo = smem_u32(f_smem_chk);
+        QCHK(a >= lo && a + 64u <= lo + (uint32_t)FT_WIN + 128u && (a & 15u) == 0u, 106u);
+    }
+#endif
     const uint4 q0 = lds128(a), q1 = lds128(a + 16u), q2 = lds128(a + 32u), q3 = lds128(a + 48u);
     const uint32_t lo = f_gather16(f_c_flags(q0.x), f_c_flags(q0.y), f_c_flags(q0.z), f_c_flags(q0.w)) |
                         f_gather16(f_c_flags(q1.x), f_c_flags(q1.y), f_c_flags(q1.z), f_c_flags(q1.w)) << 16;
@@ -286,6 +293,8 @@ __device__ __forceinline__ uint4 f_digest(const BatchDev &b, const StreamDev &st
     const uint32_t W = (st.wi + 3u) >> 2, WM = (st.wm + 3u) >> 2;   // uniform: words per span (<= 4)
     const uint32_t thr4 = ((uint32_t)b.min_qual + 33u) * 0x01010101u;
     uint32_t *slot = reinterpret_cast<uint32_t *>(st.sfx + (size_t)v * st.sfx_slot);
+    QCHK(v < st.cap_rec && 4u * (W + WM) <= st.sfx_slot && sq + ia + 4u * W + 4u <= (uint32_t)FT_WIN + 128u &&
+             qq + ia + 4u * W + 4u <= (uint32_t)FT_WIN + 128u && sq + ma + 4u * WM + 4u <= (uint32_t)FT_WIN + 128u, 107u);
     u64 key = 0;
     uint32_t nm = 0, badf = 0, lowf = 0;
     {
@@ -585,6 +594,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                         const uint32_t x = hb[h];
                         const uint32_t o0 = 64u * ((uint32_t)tid + (uint32_t)((h >> 1) * FT_NT)) + 32u * (uint32_t)(h & 1);
                         const uint32_t pos = o0 + (uint32_t)__ffs((int)x) - 1u;
+                        QCHK(!x || hi_[h] < (uint32_t)FT_PCAP, 101u);
                         sts16(a_pos + 2u * (x ? hi_[h] : (uint32_t)FT_PCAP), pos);
                         hi_[h] += x ? 1u : 0u;
                         hb[h] = x & (x - 1u);
@@ -624,6 +634,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
                     }
                     uint32_t r = found + ci - c;
                     while (m && r < 4u) {
+                        QCHK(total + r < (uint32_t)FT_PCAP, 102u);
                         s_pos[total + r] = (uint16_t)(off + (uint32_t)__ffs((int)m) - 1u);
                         m &= m - 1u;
                         ++r;
@@ -731,6 +742,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
             }
             const uint32_t nl0 = lds16(a_pos + 2u * li), nl1 = lds16(a_pos + 2u * li + 2u), nl2 = lds16(a_pos + 2u * li + 4u),
                            nl3 = lds16(a_pos + 2u * li + 6u);
+            QCHK(li + 3u < (uint32_t)FT_PCAP && hs <= nl0 && nl0 < nl1 && nl1 < nl2 && nl2 < nl3 && nl3 <= win, 103u);
             uint32_t noff, nlen;
             if (s < 2 || QUADE_F_IDXTOK) f_token(sm0, hs, nl0, noff, nlen);
             else {                                              // index reads: only whether there is a name token matters
@@ -765,6 +777,7 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         if (can) {
             for (uint32_t slot = (uint32_t)tid; slot < nslot; slot += FT_NT)     // more than one round: records < 64 bytes
                 if (parse_slot(slot, base + slot)) {
+                    QCHK(base + slot < st.cap_rec, 104u);
                     st.nv[base + slot] = o_nv;
                     st.rec[base + slot] = o_rec;
                 }
@@ -867,7 +880,10 @@ __global__ void __launch_bounds__(kTileChunk) k_tilescan(const __grid_constant__
     __syncthreads();
     for (uint32_t i = (uint32_t)warp; i < (uint32_t)kTileChunk; i += kTileChunk / 32) {
         const uint32_t ns = s_ns[i], rb = s_rb[i], sb = s_sb[i];
-        for (uint32_t j = (uint32_t)lane; j < ns; j += 32u) st.loc[rb + j] = sb + j;
+        for (uint32_t j = (uint32_t)lane; j < ns; j += 32u) {
+            QCHK(rb + j < st.cap_rec && sb + j < st.cap_rec, 105u);
+            st.loc[rb + j] = sb + j;
+        }
     }
 }
 

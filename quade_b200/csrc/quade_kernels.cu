@@ -24,6 +24,21 @@ typedef unsigned long long u64;
 
 __device__ __forceinline__ bool is_ws(uint32_t c) { return c == 0x20u || (c - 9u) <= 4u; } // Py2 str whitespace
 
+// Self-made bounds checks (compute-sanitizer is closed on this pool): a build with -DQUADE_CHECKS=1 tests every
+// shared / global store index and every window read of the hot kernels against its buffer and counts violations in
+// g_qcheck {violations, code of the first one}; quade_ctx_destroy prints the tally (tools/gpu_checks.sh).
+#if QUADE_CHECKS
+__device__ unsigned int g_qcheck[2];
+#define QCHK(cond, code)                                                                                           \
+    do {                                                                                                           \
+        if (!(cond)) {                                                                                             \
+            if (atomicAdd(&g_qcheck[0], 1u) == 0u) g_qcheck[1] = (code);                                           \
+        }                                                                                                          \
+    } while (0)
+#else
+#define QCHK(cond, code) do { } while (0)
+#endif
+
 } // namespace
 } // namespace quade
 
@@ -32,3 +47,17 @@ __device__ __forceinline__ bool is_ws(uint32_t c) { return c == 0x20u || (c - 9u
 #include "quade_bins.cuh"
 #include "quade_compact.cuh"
 #include "quade_launch.cuh"
+
+namespace quade {
+// violations counted by a QUADE_CHECKS build since the last call (0 0 in a normal build)
+void debug_check_tally(unsigned int out[2])
+{
+    out[0] = out[1] = 0u;
+#if QUADE_CHECKS
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_qcheck, sizeof(unsigned int) * 2);
+    const unsigned int z[2] = {0u, 0u};
+    cudaMemcpyToSymbol(g_qcheck, z, sizeof(z));
+#endif
+}
+} // namespace quade

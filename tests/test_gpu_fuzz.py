@@ -8,6 +8,8 @@ counts.  Every chunk goes through one context as ONE batch and again sliced into
 (per-file end-of-file flags); counters, per-bin streams, consumed bytes and skipped counts must equal the oracle's.
 Headers without a name token are generated too: both sides must refuse them (IndexError in the reference).
 """
+import os
+
 import numpy as np
 import pytest
 from hypothesis import HealthCheck, given, settings, strategies as st
@@ -74,7 +76,7 @@ def _same(r, ref, tag):
         assert r.arena(k).tobytes() == ref.out[k], tag
 
 
-@settings(max_examples=300, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+@settings(max_examples=int(os.environ.get("QUADE_FUZZ_EXAMPLES", "300")), deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
 @given(chunk(), st.lists(st.integers(1, 400), min_size=4, max_size=4))
 def test_generated_fastq_matches_the_oracle(streams, steps):
     from quade_b200 import QuadeError
