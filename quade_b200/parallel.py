@@ -67,6 +67,12 @@ def allreduce_counters(counters, device=None):
     return t.cpu().numpy()
 
 
+def any_rank_failed(failed, device=None):
+    """True on every rank if some rank reports a failure (one tiny all-reduce: the ranks agree before they meet in
+    the counters' all-reduce or a barrier, so that one rank's exception does not hang the others)."""
+    return bool(allreduce_counters(np.array([1 if failed else 0], dtype=np.int64), device)[0])
+
+
 def barrier():
     dist = _dist()
     if dist is not None and dist.get_world_size() > 1:

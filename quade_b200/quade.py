@@ -143,6 +143,7 @@ class Quade(object):
             affinity.bind_to_gpu(local_rank, self.world)      # threads and pinned pages of this rank next to its GPU
 
         print("Start parsing files: {} chunks to be parsed".format(len(self.seq_R1)))
+        failure = None
         try:
             t0 = time()
             self._open_engine()
@@ -153,10 +154,19 @@ class Quade(object):
             else:
                 self.simple_index_parser()
             Sample.FLUSH_ALL()
+        except BaseException as E:                  # noqa: B902 -- re-raised below, after the ranks have agreed
+            failure = E
         finally:
             t0 = time()
             self._close_engine()
             self._prof["close"] += time() - t0
+        if self.world > 1:
+            # a rank that failed (blank header, capacity, I/O) must not leave the others waiting in the all-reduce
+            others = parallel.any_rank_failed(failure is not None, self.device)
+            if failure is None and others:
+                raise RuntimeError("another rank of this run failed: see its output")
+        if failure is not None:
+            raise failure
 
         if self.world > 1:
             # the path's only collective: the report counters; then restore bin order by chunk index
