@@ -268,7 +268,8 @@ extern "C" int quade_ctx_create(int device, const quade_params *p, quade_ctx **o
         delete c;
         return fail(QUADE_ERR_ARG, "batch capacity too large: stream bytes and output arena must stay below 4 GiB");
     }
-    uint32_t ppb = 1024;   // pairs per histogram block: small blocks balance the persistent CTAs
+    uint32_t ppb = 4096;   // pairs per histogram block (1024 / 2048 / 4096: classify + bin scans + offsets 0.153 / 0.142 / 0.138 ms)
+    if (const char *v = getenv("QUADE_PPB")) ppb = (uint32_t)std::max(256, atoi(v));
     while (ppb < (uint32_t)c->n_bins && ppb < 65536u) ppb <<= 1;
     c->pairs_per_block = ppb;
     c->cap_blocks = (uint32_t)((c->cap_pairs + ppb - 1) / ppb);
