@@ -1,19 +1,19 @@
 #!/bin/bash
-# One GPU-box round: parity tests, bench line, ncu launch list, one full capture of the hot kernels.
+# One GPU-box round: smoke, parity tests, bench line, reference arm, ncu launch list, one full capture of the kernels.
 # usage (under gpurun): bash tools/gpu_round.sh <tag>
-tag=${1:-r01}
+tag=${1:-r02}
 mkdir -p gpurun_out
 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${tag}_smoke.log 2>&1; echo "smoke exit $?"; tail -2 gpurun_out/${tag}_smoke.log
-python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/${tag}_pytest.log
+python -m pytest tests -m gpu -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest exit $?" | tee -a gpurun_out/${tag}_pytest.log
 tail -3 gpurun_out/${tag}_pytest.log
-python bench.py --steps 20 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench exit $?"
+python bench.py --impl reference --steps 20 --warmup 3 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench.err; echo "ref exit $?"
+cat gpurun_out/${tag}_bench_ref.json | cut -c1-600
+python bench.py --steps 20 --warmup 3 > gpurun_out/${tag}_bench.json 2>> gpurun_out/${tag}_bench.err; echo "bench exit $?"
 cat gpurun_out/${tag}_bench.json
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2>> gpurun_out/${tag}_bench.err; echo "ref exit $?"
-cat gpurun_out/${tag}_bench_ref.json
 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_ncu1.log 2>&1
 echo "ncu launches exit $?"
-ncu --set full --clock-control none --import-source on -k regex:'k_frame6|k_compact3|k_classify2|k_densify|k_tilescan|k_offsets|k_binscan_blocks' -s 24 -c 8 \
+ncu --set full --clock-control none --import-source on -k regex:'k_frame|k_compact|k_classify|k_tilescan|k_offsets|k_binscan|k_pairing|k_locate' -s 40 -c 10 \
     -f -o gpurun_out/${tag}_prof python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/${tag}_ncu2.log 2>&1
 echo "ncu full exit $?"

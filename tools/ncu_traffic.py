@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""profiles/r01_traffic.json from an ncu --set full report (run here, no GPU):
-  python tools/ncu_traffic.py gpurun_out/r01c_prof.ncu-rep profiles/r01_traffic.json
+"""profiles/r02_traffic.json from an ncu --set full report (run here, no GPU):
+  python tools/ncu_traffic.py gpurun_out/r02_prof.ncu-rep profiles/r02_traffic.json
 Per kernel: DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum), duration, issue-slot use."""
 import csv
 import io
