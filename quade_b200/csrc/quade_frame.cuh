@@ -35,6 +35,11 @@ constexpr int FT_NT = FT_TILE / 64 / FT_WPT;   // threads per CTA
 constexpr int FT_NW = FT_NT / 32;
 constexpr int FT_HALO = 2048;                  // bytes after the tile that are staged as well
 constexpr int FT_WIN = FT_TILE + FT_HALO;
+#ifndef QUADE_F_SPLIT
+#define QUADE_F_SPLIT FT_WIN
+#endif
+constexpr int FT_SPLIT = QUADE_F_SPLIT;        // bytes of the first of two window copies (FT_WIN: one copy).  FT_TILE / 2 -- the threads
+                                               // start on the first half while the second is in flight -- measured no gain (0.3494 vs 0.3476 ms)
 constexpr int FT_WORDS = FT_WIN / 64;          // 64-bit bitmap words
 #ifndef QUADE_F_PCAP
 #define QUADE_F_PCAP (FT_TILE * 3 / 32)
@@ -46,9 +51,7 @@ static_assert(FT_HALO / 64 == 32, "the halo's bitmap words are scanned by one wa
 static_assert(FT_NW >= 2 && FT_NW <= 32 && FT_WIN < 65536, "line ends are listed as u16 window offsets");
 constexpr int FT_NPK = (FT_WPT + 1) / 2;       // registers that carry the line-end counts of a thread's words through the scans
 static_assert(FT_WPT >= 1 && FT_WPT <= 4 && FT_NPK * FT_NW <= 32, "warp counts live in the first misc words");
-#ifndef QUADE_F_POLL1
-#define QUADE_F_POLL1 0                        // one lane per warp spins on the copy's mbarrier: measured slower (0.504 vs 0.477 ms)
-#endif
+// measured and rejected: one lane per warp spinning on the copy's mbarrier (0.504 vs 0.477 ms)
 #ifndef QUADE_F_GUESSW
 #define QUADE_F_GUESSW 0                       // only the warps that can own a record slot guess the record phase: measured slower (0.476 vs 0.456 ms)
 #endif
@@ -402,13 +405,20 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         const uint32_t tbase = tk[2] * (uint32_t)FT_TILE, n16 = (b.st[s].n + 15u) & ~15u;
         const uint32_t bytes = n16 > tbase ? min((uint32_t)FT_WIN, n16 - tbase) : 0u;
         if (bytes) {
+            // two copies, two mbarriers: the threads start on the first half of the tile while the second is in flight
+            const uint32_t first = min(bytes, (uint32_t)FT_SPLIT);
             fence_proxy_async();
-            mbar_expect_tx(s_bar, bytes);
-            bulk_g2s(sm0, b.st[s].data + tbase, bytes, s_bar);
+            mbar_expect_tx(s_bar, first);
+            bulk_g2s(sm0, b.st[s].data + tbase, first, s_bar);
+            if (bytes > first) {
+                mbar_expect_tx(s_bar + 8u, bytes - first);
+                bulk_g2s(sm0 + first, b.st[s].data + tbase + first, bytes - first, s_bar + 8u);
+            }
         }
     };
     if (tid == 0) {
         mbar_init(s_bar, 1);
+        mbar_init(s_bar + 8u, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         s_misc[FM_NINV] = 0u;
         s_misc[FM_BLANK] = FT_NONE;
@@ -430,14 +440,14 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
         const uint32_t win = n > tbase ? min((uint32_t)FT_WIN, n - tbase) : 0u;
         const bool lastbuf = ((b.last >> s) & 1) != 0;
         const bool edge = win < (uint32_t)FT_WIN;               // the window reaches the end of the buffer
-        if (((n + 15u) & ~15u) > tbase) {                       // a copy was issued for this tile
-            if (QUADE_F_POLL1) {
-                if (lane == 0)
-                    while (!mbar_try_wait(s_bar, phase)) {}     // one lane spins ...
-                __syncwarp();
-            }
-            while (!mbar_try_wait(s_bar, phase)) {}             // ... every thread observes the completed phase once
+        const uint32_t copied = ((n + 15u) & ~15u) > tbase ? min((uint32_t)FT_WIN, ((n + 15u) & ~15u) - tbase) : 0u;
+        if (copied) {                                           // first copy of this tile
+            while (!mbar_try_wait(s_bar, phase & 1u)) {}
             phase ^= 1u;
+        }
+        if (copied > (uint32_t)FT_SPLIT && (REDO || FT_WPT == 1)) {   // the redo pass (and one-word threads) wait for all of it here
+            while (!mbar_try_wait(s_bar + 8u, (phase >> 1) & 1u)) {}
+            phase ^= 2u;
         }
 
         // 1. newline masks.  Fast pass: thread t owns the 64 bytes of the bitmap words t, t + FT_NT, ...; the four
@@ -450,6 +460,10 @@ __global__ void __launch_bounds__(FT_NT, REDO ? 1 : QUADE_F_MINB) k_frame(const 
 #pragma unroll
             for (int w = 0; w < FT_WPT; ++w) {
                 const uint32_t o0 = 64u * ((uint32_t)tid + (uint32_t)(w * FT_NT)), a = sm0 + o0;
+                if (FT_WPT > 1 && w == FT_WPT / 2 && copied > (uint32_t)FT_SPLIT) {   // second copy: the upper word rows and the halo
+                    while (!mbar_try_wait(s_bar + 8u, (phase >> 1) & 1u)) {}
+                    phase ^= 2u;
+                }
                 uint32_t r[4];
 #pragma unroll
                 for (uint32_t i = 0; i < 4; ++i) {
