@@ -23,6 +23,9 @@ namespace {
 constexpr int C3_TP = kCompactTilePairs;                  // pairs per tile (upper bound; the batch's value is in BatchState)
 static_assert(C3_TP >= 1 && C3_TP <= 8, "k_compact: one record lane per read of the tile, 16 record lanes");
 constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stream per stage
+#ifndef QUADE_C_PAIRED
+#define QUADE_C_PAIRED 1        /* phase 2 copies a pair (R1 | R2 on the two half warps) per iteration, one packed parameter block per record */
+#endif
 #ifndef QUADE_C3_HS
 #define QUADE_C3_HS 144         /* name + suffix up to 98 bytes always take the fast path (176: 130); longer ones the generic one */
 #endif
@@ -174,7 +177,19 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
             m.cls = b.cls[p];
             m.rc = b.st[k].rec[v];
             m.nlen = b.st[k].nv[v].x;
+            // ONE load through a selected pointer: written as `k ? out2[p] : out1[p]` it compiled to two predicated loads
+            // into the same register, and the second waited for the first (a quarter of the kernel's stall samples)
+            // Written like this, ptxas emits two predicated loads into one register and the second waits for the first: the
+            // warp sits out one DRAM latency here, at the top of every tile (22 % of the kernel's stall samples).  The
+            // obvious form -- one load through a selected pointer -- removes that wait and was measured SLOWER
+            // (0.665 vs 0.607 ms, A B A B on one box, with and without a sleep / time hint in the mbarrier poll): the wait
+            // overlaps the TMA copy of this tile, which is polled for right after; without it the warps spin there.
+#if QUADE_C_OOFF1
+            const uint32_t *const op = k ? b.out2 : b.out1;
+            m.ooff = op[p];
+#else
             m.ooff = k ? b.out2[p] : b.out1[p];
+#endif
             if (role == 0u && k == 0u) {                                // the pair's suffix, staged by this lane
                 const uint4 *sp = reinterpret_cast<const uint4 *>(b.suffix + (size_t)p * b.suf_cap);
                 m.suf0 = sp[0];
@@ -243,7 +258,11 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
         }
         if (cur.size0 | cur.size1) {
             const uint32_t bar = s_bar + 8u * stage;
+#ifdef QUADE_C_SLEEP
+            while (!mbar_try_wait(bar, (phase_bits >> stage) & 1u)) __nanosleep(QUADE_C_SLEEP);
+#else
             while (!mbar_try_wait(bar, (phase_bits >> stage) & 1u)) {}
+#endif
             phase_bits ^= 1u << stage;
         }
 
@@ -289,6 +308,20 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
         // values through all 32 lanes 2*tp times per tile): destination pointer of the record's first 16-byte
         // frame, number of full vectors, byte ranges of the partial first / last vector, source addresses
         if (role == 0u && rec_lane) {
+#if QUADE_C_PAIRED
+            // ONE 16-byte parameter block per record: a broadcast 128-bit shared load costs a wavefront per quarter warp
+            // whatever the addresses, so two blocks per record were 8 of the ~22 load wavefronts a record took
+            if (fast) {
+                const uint32_t endb = a + total, F1 = endb >> 4;
+                const uint32_t h0 = a, h1 = a ? (endb < 16u ? endb : 16u) : 0u;     // first partial vector [h0, h1)
+                const uint32_t t1 = (F1 > 0u || a == 0u) ? endb : 0u;               // last partial vector [16 F1, t1)
+                sts128(s_par + r * 16u, make_uint4(cur.ooff - a,                                             // frame start in the arena
+                                                   F1 | (a + J) << 16 | (srcb & 15u) << 24 | (a ? 1u : 0u) << 28,
+                                                   (hb - s_in) | (srcb - s_in + 1024u) << 16, h0 | h1 << 4 | t1 << 9));
+            } else {
+                sts128(s_par + r * 16u, make_uint4(cur.ooff, 0u, 1024u << 16, 0u));    // inactive in phase 2
+            }
+#else
             if (fast) {
                 const uint32_t endb = a + total, F1 = endb >> 4;
                 const u64 gp = (u64)(uintptr_t)(b.out[k] + (size_t)(cur.ooff - a));
@@ -300,10 +333,54 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
                 sts128(s_par + r * 32u, make_uint4(cur.ooff, 0u, 0u, 0u));          // inactive in phase 2
                 sts128(s_par + r * 32u + 16u, make_uint4(s_in, s_in, 0u, 0u));
             }
+#endif
         }
         const unsigned slow = __ballot_sync(0xffffffffu, role == 0u && written && !fast);
         __syncwarp();
 
+#if QUADE_C_PAIRED
+        // ---------------- phase 2: one PAIR per iteration, branch-free ----------------
+        // lanes 0-15 copy the pair's R1 record, lanes 16-31 its R2 record, two 16-byte vectors per lane (records up to
+        // 512 bytes in one step): half the iterations, half the parameter loads and bookkeeping per record
+        {
+            const uint32_t hw = (uint32_t)lane >> 4, l16 = (uint32_t)lane & 15u;
+            uint8_t *const obase = b.out[hw];
+#pragma unroll 2
+            for (uint32_t it = 0; it < tp; ++it) {
+                const uint4 P = lds128(s_par + (it + hw * tp) * 16u);
+                uint8_t *const gdst = obase + P.x;
+                const uint32_t F1 = P.y & 0xffffu, hend = (P.y >> 16) & 0xffu, sr = (P.y >> 24) & 15u, vlo = (P.y >> 28) & 1u;
+                const uint32_t hbi = s_in + (P.z & 0xffffu), sb = s_in + (P.z >> 16) - 1024u;
+                const uint32_t h0 = P.w & 15u, h1 = (P.w >> 4) & 31u, t1 = P.w >> 9;
+#pragma unroll
+                for (uint32_t j = 0; j < 2; ++j) {
+                    const uint32_t v = l16 + 16u * j, y0 = 16u * v;
+                    const uint32_t sa = ((y0 < hend ? hbi : sb) + y0) & ~15u;
+                    const uint4 val = shift_bytes_sel(lds128(sa), lds128(sa + 16u), sr);
+                    QCHK(!(v >= vlo && v < F1) || (sa >= s_in && sa + 32u <= s_bar), 201u);
+                    QCHK(!(v >= vlo && v < F1) || (gdst + y0 >= obase && gdst + y0 + 16u <= obase + St->out_total[hw]), 202u);
+                    if (v >= vlo && v < F1) *reinterpret_cast<uint4 *>(gdst + y0) = val;
+                }
+                if (F1 > 32u) {                                                    // records longer than 512 bytes
+#pragma unroll 1
+                    for (uint32_t v = l16 + 32u; v < F1; v += 16u) {
+                        const uint32_t sa = (sb + 16u * v) & ~15u;
+                        *reinterpret_cast<uint4 *>(gdst + 16u * v) = shift_bytes_sel(lds128(sa), lds128(sa + 16u), sr);
+                    }
+                }
+                // first partial vector: bytes [h0, h1); last one: [16 F1, t1); one byte per lane of the record's half warp
+#pragma unroll
+                for (uint32_t j = 0; j < 2; ++j) {
+                    const uint32_t y = j ? 16u * F1 + l16 : l16;
+                    const bool okb = j ? y < t1 : (y >= h0 && y < h1);
+                    const uint32_t bsrc = (y < hend ? hbi : sb) + y;
+                    QCHK(!okb || (bsrc >= s_in && bsrc < s_bar), 203u);
+                    QCHK(!okb || (gdst + y >= obase && gdst + y < obase + St->out_total[hw]), 204u);
+                    if (okb) gdst[y] = (uint8_t)lds8(bsrc);
+                }
+            }
+        }
+#else
         // ---------------- phase 2: one record per iteration, branch-free ----------------
         const uint32_t nrec = 2u * tp;
 #pragma unroll 2
@@ -335,12 +412,13 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
             QCHK(!okb || (gdst + y >= b.out[i >= tp ? 1 : 0] && gdst + y < b.out[i >= tp ? 1 : 0] + St->out_total[i >= tp ? 1 : 0]), 204u);
             if (okb) gdst[y] = (uint8_t)lds8(bsrc);
         }
+#endif
         if (slow) {                                                                // records off the fast path
 #pragma unroll 1
             for (unsigned rem = slow; rem; rem &= rem - 1u) {
                 const uint32_t i = (uint32_t)__ffs((int)rem) - 1u;                 // record slot = its role-0 lane
                 const uint32_t kk = i >= tp ? 1u : 0u, pp = tile * tp + (i - kk * tp);
-                emit_generic(b, (int)kk, pp, b.cls[pp], lds32(s_par + i * 32u), lane);
+                emit_generic(b, (int)kk, pp, b.cls[pp], lds32(s_par + i * (QUADE_C_PAIRED ? 16u : 32u)), lane);
             }
         }
         __syncwarp();
