@@ -394,7 +394,9 @@ class Quade(object):
                         want = [int(min(B, max(0.0, pairs * bpr[s] - new_tail[s][1]))) & ~15 for s in range(ns)]
                         if stalled:
                             want = [min(B, max(w, 1 << 20) * (2 ** stalled)) for w in want]
-                    want = [min(w, 2 * B - head) for w in want]
+                    # a file that is ahead of the others keeps its tail and reads nothing: tail + new bytes must fit the
+                    # carry-over room of the next batch whatever that batch consumes
+                    want = [max(0, min(w, 2 * B - head, head - new_tail[s][1])) for s, w in enumerate(want)]
                     if stalled > 8 or any(t[1] > head for t in new_tail):
                         raise IOError("a FASTQ record of chunk {} is larger than the staging buffer "
                                       "(QUADE_BATCH_BYTES={})".format(n + 1, B))

@@ -101,3 +101,59 @@ def test_overlapped_pipeline_three_chunks_many_batches_matches_oracle(tmp_path, 
     for f in got:
         with gzip.open(f, "rb") as fh:
             assert fh.read() == expect[f], f
+
+
+def _short_index_chunk(n, seed=3):
+    """n pairs whose index reads are 30-byte records (SRA-style headers, 4-base index): lines of 7.5 bytes on
+    average, five times the records per byte of the insert reads."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    keys = ["ACGT", "TTGA", "CCAT"]
+    r1, r2, i1 = [], [], []
+    for j in range(n):
+        name = b"@S.%d" % j
+        seq = bytes(rng.choice(list(b"ACGT"), 60).tolist())
+        r1.append(name + b" 1\n" + seq + b"\n+\n" + b"I" * 60 + b"\n")
+        r2.append(name + b" 2\n" + seq[::-1] + b"\n+\n" + b"F" * 60 + b"\n")
+        idx = keys[j % 3].encode() if j % 7 else b"GGGG"
+        i1.append(b"@%d\n" % (j % 1000) + idx + b"\n+\n" + (b"IIII" if j % 5 else b"I#II") + b"\n")
+    return [b"".join(r1), b"".join(r2), b"".join(i1)], keys
+
+
+def test_short_index_records_fill_batches_without_capacity_errors(tmp_path, monkeypatch):
+    """An index file of ~17-byte records beside 140-byte insert records, staged in small batches: the files are read
+    in proportion to their bytes per record, the index tiles hold more line ends than the fast pass lists (redo
+    path), and nothing overflows.  Outputs equal the oracle's."""
+    import gzip
+    from oracle import oracle as O
+    from quade_b200.quade import Quade
+    from quade_b200.sample import Sample
+    _fresh()
+    n = 40_000
+    streams, keys = _short_index_chunk(n)
+    wd = tmp_path / "run"
+    wd.mkdir()
+    monkeypatch.chdir(wd)
+    names = ["R1.fastq", "R2.fastq", "I1.fastq"]
+    for f, s in zip(names, streams):
+        (wd / f).write_bytes(s)
+    conf = ["[quality]", "minimal_qual : 20", "[fastq]", "seq_R1 : R1.fastq", "seq_R2 : R2.fastq", "index_R1 : I1.fastq",
+            "[index]", "index2 : False", "molecular1 : False", "molecular2 : False", "index1_start : 1", "index1_end : 4",
+            "[output]", "write_pass : True", "write_fail : True", "write_undetermined : True"]
+    for i, k in enumerate(keys):
+        conf += ["[sample%d]" % (i + 1), "name : S%d" % (i + 1), "index1_seq : " + k]
+    (wd / "conf.txt").write_text("\n".join(conf))
+    monkeypatch.setattr(Quade, "BATCH_BYTES", 1 << 20)
+    assert Quade(conf_file="conf.txt")() == 0
+    p = O.OracleParams(False, [(0, 4), (0, 0), (0, 0), (0, 0)], 20, keys)
+    ref = O.demux_batch(p, streams, last=True)
+    assert Sample.COUNTS() == [int(x) for x in ref.counters] and Sample.TOTAL == n
+    for b, name in enumerate(O.bin_names(["S1", "S2", "S3"])):
+        for k in range(2):
+            exp = ref.bin_bytes(k, b)
+            path = wd / ("%s_R%d.fastq.gz" % (name, k + 1))
+            if len(exp):
+                with gzip.open(path, "rb") as fh:
+                    assert fh.read() == exp, path
+            else:
+                assert not path.exists()

@@ -224,3 +224,34 @@ def test_native_gzip_sink_keeps_member_order_and_handles_stored_blocks(tmp_path)
             for k, paths in enumerate((r1, r2)):
                 with gzip.open(paths[b], "rb") as fh:
                     assert fh.read() == bytes(expect[b][k]), (level, b, k)
+
+
+def test_a_buffer_of_invalid_records_only_makes_progress(tmp_path, monkeypatch):
+    """One file starts with more records of len(seq) != len(qual) than a staging buffer holds: the reference skips them
+    in that file only (FastqReader.py:48-50); the batched host loop must pass them (consumed, counted, printed) and
+    pair what follows, not stop with 'record larger than the staging buffer'."""
+    from quade_b200.quade import Quade
+    from quade_b200.sample import Sample
+    from oracle import oracle as O
+    _fresh()
+    good = [b"@r%d\nACGTAC\n+\nIIIIII\n" % i for i in range(50)]
+    bad = [b"@b%d\nACGTAC\n+\nIIIII\n" % i for i in range(300)]
+    streams = [b"".join(bad + good), b"".join(good), b"".join(good)]
+    wd = tmp_path / "run"
+    wd.mkdir()
+    monkeypatch.chdir(wd)
+    for f, s in zip(("R1.fastq", "R2.fastq", "I1.fastq"), streams):
+        (wd / f).write_bytes(s)
+    (wd / "conf.txt").write_text("\n".join([
+        "[quality]", "minimal_qual : 20", "[fastq]", "seq_R1 : R1.fastq", "seq_R2 : R2.fastq", "index_R1 : I1.fastq",
+        "[index]", "index2 : False", "molecular1 : False", "molecular2 : False", "index1_start : 1", "index1_end : 4",
+        "[output]", "write_pass : True", "write_fail : True", "write_undetermined : True",
+        "[sample1]", "name : S1", "index1_seq : ACGT"]))
+    util.patch_host_engine(Quade, monkeypatch)
+    monkeypatch.setattr(Quade, "BATCH_BYTES", 1024)              # ~50 of the 300 invalid records per buffer
+    assert Quade(conf_file="conf.txt")() == 0
+    p = O.OracleParams(False, [(0, 4), (0, 0), (0, 0), (0, 0)], 20, ["ACGT"])
+    ref = O.demux_batch(p, streams, last=True)
+    assert ref.n_pairs == 50 and Sample.TOTAL == 50 and Sample.COUNTS() == [int(x) for x in ref.counters]
+    with gzip.open(wd / "S1_pass_R1.fastq.gz", "rb") as fh:
+        assert fh.read() == ref.bin_bytes(0, 1)
