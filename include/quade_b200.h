@@ -155,6 +155,27 @@ int quade_allreduce_counters(quade_ctx *const *ctxs, int n);
 /* CUDA stream handle (cudaStream_t) kernels are launched on, for callers that time with their own events */
 int quade_compute_stream(quade_ctx *ctx, void **stream);
 
+/* Has NO counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The bin layout stage of
+ * the pipeline (per-bin pair counts, per-bin byte ranges of the two output arenas, per-pair output offsets in input
+ * order inside a bin) as a call that allocates nothing: no cudaMalloc / cudaFree / allocating library routine, no
+ * context.  Its scratch (per-block per-bin histograms, 6 MiB) is a file-scope static __device__ array that every GPU
+ * loading the library holds until the process exits; sizes beyond the limits below are refused with
+ * QUADE_ERR_CAPACITY.  Works on the CURRENT device; all pointers are device pointers of that device:
+ *   d_bin[n_pairs]      bin of each pair, 0 .. nbins-1 (a pair with a bin >= nbins is left out of everything)
+ *   d_len1 / d_len2     output bytes of the pair's R1 / R2 record
+ *   d_bin_off           out: uint64[2][nbins + 1], start of every bin in the R1 arena, then in the R2 arena
+ *   d_counters          out: int64[nbins] pairs per bin
+ *   d_off1 / d_off2     out: uint64[n_pairs] byte offset of each pair's record in its arena; both NULL = not wanted
+ * Enqueues on `stream` (a cudaStream_t, NULL = the default stream) and returns without synchronising.  Every call on a
+ * device shares the scratch, which keeps the last call's contents (each call rewrites all it reads, nothing needs
+ * clearing): calls that OVERLAP on one GPU -- two streams, no dependency between them -- race on it. */
+#define QUADE_STATIC_MAX_PAIRS (1u << 20)
+#define QUADE_STATIC_MAX_BINS 1024
+int quade_bin_offsets_static(const uint32_t *d_bin, const uint32_t *d_len1, const uint32_t *d_len2, uint64_t n_pairs,
+                             int32_t nbins, uint64_t *d_bin_off, int64_t *d_counters, uint64_t *d_off1, uint64_t *d_off2,
+                             void *stream);
+
 #ifdef __cplusplus
 }
 #endif

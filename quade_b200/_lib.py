@@ -14,7 +14,8 @@ K_NAMES = ["frame", "tilescan", "pairing", "classify", "binscan", "offsets", "co
 K_COUNT = len(K_NAMES)
 SYMBOLS = ["quade_version", "quade_last_error", "quade_device_count", "quade_host_alloc", "quade_host_free",
            "quade_ctx_create", "quade_ctx_destroy", "quade_ctx_set_samples", "quade_submit", "quade_peek", "quade_collect",
-           "quade_counters", "quade_counters_reset", "quade_allreduce_counters", "quade_compute_stream"]
+           "quade_counters", "quade_counters_reset", "quade_allreduce_counters", "quade_compute_stream",
+           "quade_bin_offsets_static"]
 
 
 class Params(C.Structure):
@@ -77,6 +78,7 @@ def lib():
     L.quade_counters_reset.argtypes = [vp]
     L.quade_allreduce_counters.argtypes = [C.POINTER(vp), C.c_int]
     L.quade_compute_stream.argtypes = [vp, C.POINTER(vp)]
+    L.quade_bin_offsets_static.argtypes = [vp, vp, vp, C.c_uint64, C.c_int32, vp, vp, vp, vp, vp]
     for name in SYMBOLS:
         if name not in ("quade_version", "quade_last_error"):
             getattr(L, name).restype = C.c_int

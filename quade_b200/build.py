@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.environ.get("QUADE_LIB_PATH") or os.path.join(HERE, "libquade_b200.so")   # override: A/B builds of kernel variants
-SOURCES = ["quade_kernels.cu", "quade_api.cu"]
+SOURCES = ["quade_kernels.cu", "quade_api.cu", "quade_static.cu"]
 DEPS = SOURCES + sorted(f for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inc"))) + [os.path.join("..", "..", "include", "quade_b200.h")]
 #: the synthetic-data generator is test / benchmark infrastructure: its own library, never linked into the product
 SYNTH_LIB = os.path.join(HERE, "libquade_synth.so")

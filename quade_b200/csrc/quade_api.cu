@@ -24,6 +24,10 @@ static int fail(int code, const char *fmt, ...)
     return code;
 }
 
+namespace quade {
+void set_last_error(const char *text) { snprintf(g_err, sizeof(g_err), "%s", text); }
+} // namespace quade
+
 #define CU(call)                                                                                                   \
     do {                                                                                                           \
         cudaError_t e_ = (call);                                                                                   \

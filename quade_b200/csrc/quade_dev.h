@@ -138,6 +138,7 @@ void launch_offsets(const BatchDev &b, cudaStream_t s);
 void launch_compact(const BatchDev &b, cudaStream_t s);
 size_t classify_smem_bytes(const BatchDev &b, bool *table_in_smem);
 void debug_check_tally(unsigned int out[2]);   // QUADE_CHECKS builds: {violations, first code}
+void set_last_error(const char *text);         // quade_api.cu: the calling thread's quade_last_error() text (for quade_static.cu)
 
 #ifndef QUADE_F_TILE
 #define QUADE_F_TILE 32768
