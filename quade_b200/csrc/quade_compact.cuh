@@ -34,9 +34,13 @@ constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stre
 #endif
 constexpr int C3_HS = QUADE_C3_HS;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
 constexpr int C3_SUFV = QUADE_C3_SUFV;                // staged suffix: up to 64 bytes per pair
-constexpr int C3_STAGES = 1;               // 1: more resident warps hide the copy latency; 2: per-warp prefetch
+#ifndef QUADE_C3_STAGES
+#define QUADE_C3_STAGES 1
+#endif
+constexpr int C3_STAGES = QUADE_C3_STAGES;    // 1: more resident warps hide the copy latency; 2: per-warp prefetch
 constexpr int C3_IN_BYTES = C3_STAGES * 2 * (C3_CAP + 32);
-constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * 32 + 32;
+constexpr int C3_PAR = QUADE_C_PAIRED ? 16 : 32;  // phase-2 parameter bytes per record
+constexpr int C3_SMEM = C3_IN_BYTES + 2 * C3_TP * C3_HS + C3_TP * C3_SUFV * 16 + 2 * C3_TP * C3_PAR + 32;
 
 // shared -> shared copy of n bytes, any alignment on both sides, full destination words by funnel shift
 __device__ __forceinline__ void seg_copy(uint32_t dst, uint32_t src, uint32_t n)
@@ -147,8 +151,8 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
     const uint32_t s_in = sm0;                                         // [stage][stream][C3_CAP + 32]
     const uint32_t s_head = s_in + C3_IN_BYTES;                        // [2*TP][C3_HS]
     const uint32_t s_suf = s_head + 2 * C3_TP * C3_HS;                 // [TP][64]
-    const uint32_t s_par = s_suf + C3_TP * C3_SUFV * 16;               // [2*TP] 2 x uint4: phase-2 parameters
-    const uint32_t s_bar = s_par + 2 * C3_TP * 32;                     // 2 mbarriers
+    const uint32_t s_par = s_suf + C3_TP * C3_SUFV * 16;               // [2*TP] phase-2 parameters
+    const uint32_t s_bar = s_par + 2 * C3_TP * C3_PAR;                 // 2 mbarriers
     if (lane == 0) {
         mbar_init(s_bar, 1);
         mbar_init(s_bar + 8, 1);

@@ -46,6 +46,7 @@ __device__ unsigned int g_qcheck[2];
 #include "quade_classify.cuh"
 #include "quade_bins.cuh"
 #include "quade_compact.cuh"
+#include "quade_compact2.cuh"
 #include "quade_launch.cuh"
 
 namespace quade {

@@ -1,11 +1,15 @@
 // quade_launch.cuh -- kernel launchers (included by quade_kernels.cu)
 #pragma once
 
+#ifndef QUADE_COMPACT2
+#define QUADE_COMPACT2 0          /* 1: k_compact2 (stream ping-pong schedule, measured 0.643 ms) instead of k_compact (0.608 ms) */
+#endif
+
 namespace quade {
 // ------------------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------------------
-static int g_sms = 0, g_occ_frame = 0, g_occ_compact = 0;
+static int g_sms = 0, g_occ_frame = 0, g_occ_compact = 0, g_occ_compact2 = 0;
 static int g_f_ctas = 0, g_c_ctas = 0;      // CTAs per SM when k_frame and k_compact share the SMs (0: all that fit)
 
 static void init_launch_config()
@@ -27,6 +31,9 @@ static void init_launch_config()
     cudaFuncSetAttribute(k_compact, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C3_SMEM * C3_WPC));
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact, k_compact, 32 * C3_WPC, C3_SMEM * C3_WPC);
     if (g_occ_compact < 1) g_occ_compact = 1;
+    cudaFuncSetAttribute(k_compact2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(C4_SMEM * C4_WPC));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_occ_compact2, k_compact2, 32 * C4_WPC, C4_SMEM * C4_WPC);
+    if (g_occ_compact2 < 1) g_occ_compact2 = 1;
 }
 
 // fast pass: independent tiles into scratch
@@ -95,10 +102,17 @@ void launch_offsets(const BatchDev &b, cudaStream_t s)
 void launch_compact(const BatchDev &b, cudaStream_t s)
 {
     init_launch_config();
+#if QUADE_COMPACT2
+    uint32_t grid = (uint32_t)(g_sms * g_occ_compact2);
+    if (grid > b.cap_pairs) grid = b.cap_pairs;
+    if (grid < 1) grid = 1;
+    k_compact2<<<grid, 32 * C4_WPC, C4_SMEM * C4_WPC, s>>>(b);
+#else
     uint32_t grid = (uint32_t)(g_sms * (g_c_ctas > 0 && g_c_ctas < g_occ_compact ? g_c_ctas : g_occ_compact));
     if (grid > b.cap_pairs) grid = b.cap_pairs;
     if (grid < 1) grid = 1;
     k_compact<<<grid, 32 * C3_WPC, C3_SMEM * C3_WPC, s>>>(b);
+#endif
 }
 
 } // namespace quade
