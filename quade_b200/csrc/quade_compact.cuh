@@ -26,12 +26,16 @@ constexpr int C3_CAP = kCompactStageBytes;              // staged bytes per stre
 #ifndef QUADE_C_PAIRED
 #define QUADE_C_PAIRED 1        /* phase 2 copies a pair (R1 | R2 on the two half warps) per iteration, one packed parameter block per record */
 #endif
+#ifndef QUADE_C_UNROLL
+#define QUADE_C_UNROLL 8         /* phase 2 unrolled over the pairs of a tile: 1 / 2 / 4 / 8 measured 0.609 / 0.607 / 0.612 / 0.599 ms */
+#endif
 #ifndef QUADE_C3_HS
 #define QUADE_C3_HS 144         /* name + suffix up to 98 bytes always take the fast path (176: 130); longer ones the generic one */
 #endif
 #ifndef QUADE_C3_SUFV
 #define QUADE_C3_SUFV 4
 #endif
+constexpr int C3_UNROLL = QUADE_C_UNROLL;
 constexpr int C3_HS = QUADE_C3_HS;                // HEAD slot stride: 16-byte multiple (slots are read back as vectors)
 constexpr int C3_SUFV = QUADE_C3_SUFV;                // staged suffix: up to 64 bytes per pair
 #ifndef QUADE_C3_STAGES
@@ -349,7 +353,7 @@ __global__ void __launch_bounds__(32 * C3_WPC) k_compact(const __grid_constant__
         {
             const uint32_t hw = (uint32_t)lane >> 4, l16 = (uint32_t)lane & 15u;
             uint8_t *const obase = b.out[hw];
-#pragma unroll 2
+#pragma unroll C3_UNROLL
             for (uint32_t it = 0; it < tp; ++it) {
                 const uint4 P = lds128(s_par + (it + hw * tp) * 16u);
                 uint8_t *const gdst = obase + P.x;
