@@ -41,6 +41,17 @@ int qio_sink_wait(qio_sink *s, uint64_t ticket);
 int qio_sink_stats(qio_sink *s, uint64_t *bytes_in, uint64_t *bytes_out);
 const char *qio_last_error(void);
 
+/* The reading side (src/pyFastq/FastqReader.py:30: a path ending in "gz" is opened with gzip): a host thread per
+ * file inflates ahead into `depth` blocks of `block_bytes`, with no interpreter in the loop, while the caller drains
+ * them into its (pinned) staging buffers.  Any number of concatenated gzip members is one stream, as for Python's
+ * gzip module (the reference's own writer appends a member per flush); zero padding after the last member is ignored. */
+typedef struct qio_reader qio_reader;
+int qio_reader_open(const char *path, uint64_t block_bytes, int depth, qio_reader **out);
+/* up to `cap` decompressed bytes into dst; waits for data; *got = 0 only at the end of the stream.  A corrupt or
+ * truncated file gives QIO_ERR_ZLIB once the bytes in front of the damage have been handed out. */
+int qio_reader_read(qio_reader *r, uint8_t *dst, uint64_t cap, uint64_t *got);
+int qio_reader_close(qio_reader *r);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,12 +1,13 @@
 """ctypes binding of libquade_io.so (include/quade_io.h): the parallel gzip-member writer behind FastqWriter."""
 import ctypes as C
+import os
 
 import numpy as np
 
 from . import build as _build
 
 SYMBOLS = ["qio_sink_create", "qio_sink_destroy", "qio_sink_set_paths", "qio_sink_append", "qio_sink_wait",
-           "qio_sink_stats", "qio_last_error"]
+           "qio_sink_stats", "qio_last_error", "qio_reader_open", "qio_reader_read", "qio_reader_close"]
 _LIB = None
 
 
@@ -22,6 +23,9 @@ def lib():
         L.qio_sink_append.argtypes = [vp, vp, vp, vp, vp, u64p]
         L.qio_sink_wait.argtypes = [vp, C.c_uint64]
         L.qio_sink_stats.argtypes = [vp, u64p, u64p]
+        L.qio_reader_open.argtypes = [C.c_char_p, C.c_uint64, C.c_int, C.POINTER(vp)]
+        L.qio_reader_read.argtypes = [vp, vp, C.c_uint64, u64p]
+        L.qio_reader_close.argtypes = [vp]
         for n in SYMBOLS:
             if n != "qio_last_error":
                 getattr(L, n).restype = C.c_int
@@ -77,6 +81,38 @@ class GzipSink:
             self._L.qio_sink_destroy(self._s)
             self._s = C.c_void_p(None)
             self._keep.clear()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class GzipReader:
+    """A gzip file inflated ahead by a host thread of libquade_io.so (no interpreter in the loop); readinto(arr) drains
+    the decompressed bytes into a numpy uint8 view.  src/pyFastq/FastqReader.py:30."""
+
+    def __init__(self, path, block_bytes=8 << 20, depth=4):
+        self._L = lib()
+        self._r = C.c_void_p(None)
+        _check(self._L.qio_reader_open(os.fsencode(path), int(block_bytes), int(depth), C.byref(self._r)))
+
+    def readinto(self, arr):
+        """Fills arr as far as the stream allows; fewer bytes than arr.size means the end of the stream."""
+        want, done, got = int(arr.size), 0, C.c_uint64(0)
+        base = arr.ctypes.data
+        while done < want:
+            _check(self._L.qio_reader_read(self._r, C.c_void_p(base + done), want - done, C.byref(got)))
+            if got.value == 0:
+                break
+            done += got.value
+        return done
+
+    def close(self):
+        if self._r:
+            self._L.qio_reader_close(self._r)
+            self._r = C.c_void_p(None)
 
     def __del__(self):
         try:

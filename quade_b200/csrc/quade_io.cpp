@@ -258,3 +258,185 @@ extern "C" int qio_sink_stats(qio_sink *s, uint64_t *bytes_in, uint64_t *bytes_o
     if (bytes_out) *bytes_out = s->bytes_out.load();
     return QIO_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// reader: one inflating thread per gzip file, a ring of decompressed blocks
+// ---------------------------------------------------------------------------------------------------------------
+struct qio_reader {
+    int fd = -1;
+    std::string path;
+    size_t block_bytes = 0;
+    std::thread worker;
+    std::mutex mu;
+    std::condition_variable cv_full, cv_free;      // a block was filled / a block was handed back
+    std::deque<std::vector<uint8_t>> full;         // filled blocks, oldest first
+    std::vector<std::vector<uint8_t>> spare;       // blocks to fill
+    bool done = false, stop = false;               // producer finished (end of stream or error) / consumer closes
+    int error_code = QIO_OK;
+    std::string error;
+    std::vector<uint8_t> cur;                      // block being drained by the consumer
+    size_t cur_off = 0;
+};
+
+namespace {
+
+void reader_main(qio_reader *r)
+{
+    z_stream z;
+    memset(&z, 0, sizeof(z));
+    std::string err;
+    int code = QIO_OK;
+    if (inflateInit2(&z, 15 + 32 /* gzip or zlib header, detected */) != Z_OK) {
+        err = "inflateInit2 failed";
+        code = QIO_ERR_ZLIB;
+    }
+    std::vector<uint8_t> in(1u << 20);
+    bool in_member = false, any_member = false, eof_in = false;
+    std::vector<uint8_t> blk;
+    size_t filled = 0;
+    auto take_spare = [&]() -> bool {               // false: the consumer is closing
+        std::unique_lock<std::mutex> lk(r->mu);
+        r->cv_free.wait(lk, [&] { return r->stop || !r->spare.empty(); });
+        if (r->stop) return false;
+        blk = std::move(r->spare.back());
+        r->spare.pop_back();
+        blk.resize(r->block_bytes);
+        filled = 0;
+        return true;
+    };
+    auto push_block = [&]() {
+        blk.resize(filled);
+        {
+            std::lock_guard<std::mutex> lk(r->mu);
+            r->full.push_back(std::move(blk));
+        }
+        r->cv_full.notify_one();
+        blk = std::vector<uint8_t>();
+        filled = 0;
+    };
+    bool have_blk = code == QIO_OK && take_spare();
+    while (code == QIO_OK && have_blk) {
+        if (z.avail_in == 0 && !eof_in) {
+            ssize_t n;
+            do n = read(r->fd, in.data(), in.size()); while (n < 0 && errno == EINTR);
+            if (n < 0) {
+                err = "read " + r->path + ": " + strerror(errno);
+                code = QIO_ERR_IO;
+                break;
+            }
+            if (n == 0) eof_in = true;
+            z.next_in = in.data();
+            z.avail_in = (uInt)n;
+        }
+        if (!in_member) {
+            // between members: zero padding is skipped (Python's gzip does), anything else must be a new member
+            while (z.avail_in && *z.next_in == 0 && any_member) { ++z.next_in; --z.avail_in; }
+            if (z.avail_in == 0) {
+                if (eof_in) break;                   // clean end of the stream
+                continue;
+            }
+            if (any_member) inflateReset(&z);
+            in_member = any_member = true;
+        }
+        if (z.avail_in == 0 && eof_in) {
+            err = "unexpected end of file inside a gzip member: " + r->path;
+            code = QIO_ERR_ZLIB;
+            break;
+        }
+        z.next_out = blk.data() + filled;
+        z.avail_out = (uInt)std::min<size_t>(r->block_bytes - filled, 0x40000000u);
+        const uInt before = z.avail_out;
+        const int rc = inflate(&z, Z_NO_FLUSH);
+        filled += before - z.avail_out;
+        if (rc == Z_STREAM_END) in_member = false;
+        else if (rc != Z_OK && rc != Z_BUF_ERROR) {
+            err = std::string("inflate failed (") + (z.msg ? z.msg : "corrupt data") + "): " + r->path;
+            code = QIO_ERR_ZLIB;
+            break;
+        }
+        if (filled == r->block_bytes) {
+            push_block();
+            have_blk = take_spare();
+        }
+    }
+    if (have_blk && filled) push_block();            // the bytes in front of an error are still good
+    inflateEnd(&z);
+    {
+        std::lock_guard<std::mutex> lk(r->mu);
+        r->done = true;
+        if (code != QIO_OK) {
+            r->error_code = code;
+            r->error = err;
+        }
+    }
+    r->cv_full.notify_all();
+}
+
+} // namespace
+
+extern "C" int qio_reader_open(const char *path, uint64_t block_bytes, int depth, qio_reader **out)
+{
+    if (!path || !out || block_bytes < 4096 || block_bytes > (1ull << 30) || depth < 1 || depth > 4096)
+        return fail(QIO_ERR_ARG, "path/out is NULL, or block_bytes not in 4 KiB..1 GiB, or depth not in 1..4096");
+    const int fd = open(path, O_RDONLY | O_CLOEXEC);
+    if (fd < 0) return fail(QIO_ERR_IO, "open %s: %s", path, strerror(errno));
+    qio_reader *r = new qio_reader();
+    r->fd = fd;
+    r->path = path;
+    r->block_bytes = (size_t)block_bytes;
+    r->spare.resize((size_t)depth + 1);              // blocks are sized when they are first filled
+    r->worker = std::thread(reader_main, r);
+    *out = r;
+    return QIO_OK;
+}
+
+extern "C" int qio_reader_read(qio_reader *r, uint8_t *dst, uint64_t cap, uint64_t *got)
+{
+    if (!r || !got || (cap && !dst)) return fail(QIO_ERR_ARG, "reader/dst/got is NULL");
+    uint64_t done = 0;
+    while (done < cap) {
+        if (r->cur_off == r->cur.size()) {
+            std::unique_lock<std::mutex> lk(r->mu);
+            if (r->cur.capacity()) {                                 // hand the drained block back (its size stays: no refill)
+                r->spare.push_back(std::move(r->cur));
+                r->cur = std::vector<uint8_t>();
+                r->cv_free.notify_one();
+            }
+            r->cur_off = 0;
+            if (done) {                                              // never wait with bytes in hand
+                if (r->full.empty()) break;
+            } else {
+                r->cv_full.wait(lk, [&] { return r->done || !r->full.empty(); });
+            }
+            if (r->full.empty()) {                                   // producer finished
+                if (r->error_code != QIO_OK) {
+                    *got = 0;
+                    return fail(r->error_code, "%s", r->error.c_str());
+                }
+                break;
+            }
+            r->cur = std::move(r->full.front());
+            r->full.pop_front();
+        }
+        const size_t n = (size_t)std::min<uint64_t>(cap - done, r->cur.size() - r->cur_off);
+        memcpy(dst + done, r->cur.data() + r->cur_off, n);
+        r->cur_off += n;
+        done += n;
+    }
+    *got = done;
+    return QIO_OK;
+}
+
+extern "C" int qio_reader_close(qio_reader *r)
+{
+    if (!r) return QIO_OK;
+    {
+        std::lock_guard<std::mutex> lk(r->mu);
+        r->stop = true;
+    }
+    r->cv_free.notify_all();
+    if (r->worker.joinable()) r->worker.join();
+    if (r->fd >= 0) close(r->fd);
+    delete r;
+    return QIO_OK;
+}

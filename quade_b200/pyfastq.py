@@ -10,7 +10,6 @@ import gzip
 import os
 import stat
 import threading
-import queue
 from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
@@ -33,8 +32,10 @@ class FastqReader:
     """Byte stager over one FASTQ file.
 
     readinto(arr) fills a numpy uint8 view (normally a slice of a PinnedBuffer) and returns the number of bytes
-    stored; `eof` turns True once the file is exhausted.  With prefetch=True a helper thread keeps decompressed
-    blocks ready so that inflating the next block overlaps the GPU work on the current batch.
+    stored; `eof` turns True once the file is exhausted.  A gzip file is inflated ahead by a host thread of
+    libquade_io.so (`depth` blocks of BLOCK bytes), so that inflating overlaps the GPU work on the current batch and
+    the files of the chunks opened ahead inflate side by side; prefetch=False keeps Python's gzip module in the
+    calling thread (the form the native reader is tested against).
     """
 
     BLOCK = 8 << 20
@@ -44,7 +45,13 @@ class FastqReader:
         self.path = fastq_file
         # same rule as the reference: FastqReader.py:30
         self._plain = fastq_file[-2:] != "gz"
-        self._fh = open(fastq_file, "rb", buffering=0) if self._plain else gzip.open(fastq_file, "rb")
+        self._native = None
+        if not self._plain and prefetch:
+            from ._io import GzipReader
+            self._native = GzipReader(fastq_file, self.BLOCK, depth)
+            self._fh = None
+        else:
+            self._fh = open(fastq_file, "rb", buffering=0) if self._plain else gzip.open(fastq_file, "rb")
         self._size = None          # regular plain files: size known, slices are pread() in parallel
         self._pos = 0
         if self._plain:
@@ -55,34 +62,20 @@ class FastqReader:
         self.eof = False
         self.bytes_read = 0
         self._pending = None       # (memoryview, offset) of a block partly handed out
-        self._q = None
-        if prefetch:
-            self._q = queue.Queue(maxsize=depth)
-            self._t = threading.Thread(target=self._pump, daemon=True)
-            self._t.start()
-
-    def _pump(self):
-        try:
-            while True:
-                blk = self._fh.read(self.BLOCK)
-                self._q.put(blk)
-                if not blk:
-                    return
-        except Exception as e:  # surfaced by readinto() on the consumer side
-            self._q.put(e)
 
     def _next_block(self):
-        if self._q is not None:
-            blk = self._q.get()
-            if isinstance(blk, Exception):
-                raise blk
-            return blk
         return self._fh.read(self.BLOCK)
 
     def readinto(self, arr):
         """Fill `arr` (numpy uint8, C-contiguous) as far as the file allows; returns bytes written."""
         want = int(arr.size)
         done = 0
+        if self._native is not None:
+            done = self._native.readinto(arr) if not self.eof else 0
+            if done < want:
+                self.eof = True
+            self.bytes_read += done
+            return done
         if self._plain and self._size is not None:
             want = min(want, self._size - self._pos)
             mv = memoryview(arr)
@@ -140,7 +133,10 @@ class FastqReader:
 
     def close(self):
         try:
-            self._fh.close()
+            if self._native is not None:
+                self._native.close()
+            else:
+                self._fh.close()
         except Exception:
             pass
 

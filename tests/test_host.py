@@ -7,6 +7,7 @@ import shutil
 import subprocess
 import sys
 
+import numpy as np
 import pytest
 
 from tests import util
@@ -255,3 +256,74 @@ def test_a_buffer_of_invalid_records_only_makes_progress(tmp_path, monkeypatch):
     assert ref.n_pairs == 50 and Sample.TOTAL == 50 and Sample.COUNTS() == [int(x) for x in ref.counters]
     with gzip.open(wd / "S1_pass_R1.fastq.gz", "rb") as fh:
         assert fh.read() == ref.bin_bytes(0, 1)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# native gzip reader (libquade_io.so) against Python's gzip module
+# ---------------------------------------------------------------------------------------------------------------
+def _drain(reader, sizes):
+    out, i = bytearray(), 0
+    while not reader.eof:
+        buf = np.empty(sizes[i % len(sizes)], dtype=np.uint8)
+        n = reader.readinto(buf)
+        out += buf[:n].tobytes()
+        i += 1
+    return bytes(out)
+
+
+def test_native_gzip_reader_matches_pythons_gzip(tmp_path, monkeypatch):
+    import gzip
+    from quade_b200.pyfastq import FastqReader
+    rng = np.random.default_rng(5)
+    text = b"".join(b"@r%d\n%s\n+\n%s\n" % (i, bytes(rng.choice(list(b"ACGT"), 40)), bytes(rng.integers(35, 70, 40, dtype=np.uint8)))
+                    for i in range(6000))
+    cases = {}
+    cases["one_member"] = gzip.compress(text, 1)
+    cut = [0, 1000, 1001, 70000, len(text) // 2, len(text)]
+    cases["members"] = b"".join(gzip.compress(text[a:b], 6) for a, b in zip(cut, cut[1:]))      # an empty member too
+    cases["members_20"] = b"".join(gzip.compress(text[a:a + 1800], 1) for a in range(0, len(text), 1800))
+    cases["padded"] = gzip.compress(text, 9) + b"\0" * 777
+    cases["empty_file"] = b""
+    cases["empty_member"] = gzip.compress(b"")
+    monkeypatch.setattr(FastqReader, "BLOCK", 4096)                     # many blocks: the ring turns over
+    for name, blob in cases.items():
+        p = tmp_path / (name + ".fastq.gz")
+        p.write_bytes(blob)
+        want = gzip.decompress(blob) if blob else b""
+        for depth, sizes in ((1, [100000]), (3, [1, 4095, 4096, 4097, 50000]), (64, [1 << 20])):
+            r = FastqReader(str(p), depth=depth)
+            assert r._native is not None
+            assert _drain(r, sizes) == want, (name, depth)
+            assert r.readinto(np.empty(10, dtype=np.uint8)) == 0 and r.eof
+            r.close()
+        r = FastqReader(str(p), prefetch=False)                         # Python's gzip in the calling thread: same bytes
+        assert _drain(r, [65536]) == want, name
+        r.close()
+
+
+def test_native_gzip_reader_reports_damage_after_the_good_bytes(tmp_path, monkeypatch):
+    import gzip
+    from quade_b200.pyfastq import FastqReader
+    text = bytes(np.random.default_rng(6).integers(33, 126, 300000, dtype=np.uint8))
+    blob = gzip.compress(text, 1)
+    monkeypatch.setattr(FastqReader, "BLOCK", 8192)
+    for name, bad in (("truncated", blob[:len(blob) // 2]), ("garbage_after", blob + b"not a member"),
+                      ("bad_crc", blob[:-8] + b"\x00\x00\x00\x00" + blob[-4:]), ("not_gzip", b"@r1\nACGT\n+\nIIII\n")):
+        p = tmp_path / (name + ".gz")
+        p.write_bytes(bad)
+        r = FastqReader(str(p))
+        got = bytearray()
+        with pytest.raises(IOError):
+            while not r.eof:
+                buf = np.empty(50000, dtype=np.uint8)
+                n = r.readinto(buf)
+                got += buf[:n].tobytes()
+        assert text.startswith(bytes(got)), name                        # nothing wrong was handed out before the error
+        if name == "truncated":
+            assert len(got) > 0
+        r.close()
+    r = FastqReader(str(tmp_path / "truncated.gz"))                     # closing with blocks still in flight
+    r.readinto(np.empty(10, dtype=np.uint8))
+    r.close()
+    with pytest.raises(IOError):
+        FastqReader(str(tmp_path / "missing.gz"))
