@@ -1,5 +1,5 @@
 /*
- * quade_io.h -- C-ABI of libquade_io.so: the host output sink of the B200 build.
+ * quade_io.h -- C-ABI of libquade_io.so: the host file side of the B200 build (output sink, gzip input reader).
  *
  * Replaces the file side of the reference's FastqWriter (src/FastqWriter.py:76-90): every flush there opens the
  * bin's `<name>_R1.fastq.gz` / `_R2.fastq.gz` with gzip "ab" and appends one gzip member.  Here a batch's bins

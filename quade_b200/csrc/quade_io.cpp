@@ -1,4 +1,5 @@
-// quade_io.cpp -- libquade_io.so (include/quade_io.h): parallel gzip-member writer for the per-bin output files.
+// quade_io.cpp -- libquade_io.so (include/quade_io.h): parallel gzip-member writer for the per-bin output files and
+// the inflating reader of gzip input files (src/pyFastq/FastqReader.py:30).
 // Host C++ only (zlib, threads); no CUDA.  Replaces the file side of src/FastqWriter.py:83-90.
 #include "../../include/quade_io.h"
 
