@@ -145,6 +145,10 @@ class Quade(object):
         print("Start parsing files: {} chunks to be parsed".format(len(self.seq_R1)))
         failure = None
         try:
+            # the readers of the first chunks start now: gzip files inflate (libquade_io.so threads) while the CUDA
+            # context and the pinned buffers are set up
+            chunks, mine = self._chunk_plan()
+            self._open_ahead(chunks, mine[:1 + self.CHUNKS_AHEAD], deep_first=True)
             t0 = time()
             self._open_engine()
             Sample.SINK = self._make_sink()
@@ -193,8 +197,7 @@ class Quade(object):
 
     def double_index_parser(self):
         """Quade.py:195-224: chunk n = n-th file of seq_R1, seq_R2, index_R1, index_R2"""
-        chunks = list(zip(self.seq_R1, self.seq_R2, self.index_R1, self.index_R2))
-        mine = parallel.chunks_of_rank(len(chunks), self.rank, self.world)
+        chunks, mine = self._chunk_plan()
         for i, n in enumerate(mine):
             print("Start parsing chunk {}".format(n + 1))
             self._open_ahead(chunks, mine[i:i + 1 + self.CHUNKS_AHEAD])
@@ -203,8 +206,7 @@ class Quade(object):
 
     def simple_index_parser(self):
         """Quade.py:226-254"""
-        chunks = list(zip(self.seq_R1, self.seq_R2, self.index_R1))
-        mine = parallel.chunks_of_rank(len(chunks), self.rank, self.world)
+        chunks, mine = self._chunk_plan()
         for i, n in enumerate(mine):
             print("Start parsing chunk {}/{}".format(n + 1, len(self.seq_R1)))
             self._open_ahead(chunks, mine[i:i + 1 + self.CHUNKS_AHEAD])
@@ -230,13 +232,24 @@ class Quade(object):
                                         max_stream_bytes=2 * self.BATCH_BYTES, n_slots=self.N_SLOTS)
         return self._engine
 
-    def _open_ahead(self, chunks, which):
-        """FastqReader objects of the chunks in `which` (the current one first), opened now."""
+    def _chunk_plan(self):
+        """(file tuples of all chunks, indices of the chunks of this rank): chunk n = n-th file of every list
+        (Quade.py:195-198, :226-229)"""
+        if self.idx2:
+            chunks = list(zip(self.seq_R1, self.seq_R2, self.index_R1, self.index_R2))
+        else:
+            chunks = list(zip(self.seq_R1, self.seq_R2, self.index_R1))
+        return chunks, parallel.chunks_of_rank(len(chunks), self.rank, self.world)
+
+    def _open_ahead(self, chunks, which, deep_first=False):
+        """FastqReader objects of the chunks in `which` (the current one first), opened now.  The current chunk is
+        drained as it inflates and needs little read-ahead, unless nobody drains it yet (deep_first: start-up)."""
         if not hasattr(self, "_opened"):
             self._opened = {}
         for n in which:
             if n not in self._opened:
-                self._opened[n] = [FastqReader(f, depth=self.AHEAD_BLOCKS if n != which[0] else 4) for f in chunks[n]]
+                deep = deep_first or n != which[0]
+                self._opened[n] = [FastqReader(f, depth=self.AHEAD_BLOCKS if deep else 4) for f in chunks[n]]
 
     def _make_sink(self):
         from .fastq_writer import BinSink
