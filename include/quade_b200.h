@@ -136,11 +136,13 @@ int quade_ctx_set_samples(quade_ctx *ctx, const uint8_t *keys, const uint32_t *k
 /* asynchronous: H2D copy (copy stream) -> kernels (compute stream); returns once everything is enqueued */
 int quade_submit(quade_ctx *ctx, const quade_batch *batch);
 /* blocks until the kernels of the oldest submitted batch are done and describes it -- n_pairs, consumed[], n_skipped[],
- * bin_off, counters, errors; out[] stays NULL -- WITHOUT copying its bins back and without releasing it: the caller
- * learns the carry-over (consumed[]) early, submits the next batch, and only then collects this one, so that the
- * D2H copy of batch N runs beside the H2D copy and the kernels of batch N+1 */
+ * bin_off, counters, errors; out[] stays NULL -- without releasing it and without waiting for its bins: their D2H
+ * copy is only ENQUEUED here (host contexts).  The caller learns the carry-over (consumed[]) early, submits the next
+ * batch, and only then collects this one, so that the D2H copy of batch N runs beside the H2D copy and the kernels of
+ * batch N+1 and beside the caller's own work */
 int quade_peek(quade_ctx *ctx, quade_result *res);
-/* blocks until the oldest submitted batch is done, copies its bins back (D2H stream) and describes them */
+/* blocks until the oldest submitted batch is done and its bins are back (D2H stream; the copy is enqueued here unless
+ * quade_peek already did) and describes them */
 int quade_collect(quade_ctx *ctx, quade_result *res);
 
 /* cumulative pair counts since ctx creation / reset: int64[1+2*n_samples] in bin order */

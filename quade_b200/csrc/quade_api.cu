@@ -47,6 +47,7 @@ struct Slot {
     BatchDev dev;
     // pinned host mirrors
     uint8_t *h_out[2] = {nullptr, nullptr};
+    bool d2h_issued = false;      // the output copy of the batch in this slot has been enqueued (quade_peek / quade_collect)
     BatchState *h_state = nullptr;
     unsigned long long *h_bin_off = nullptr;
     long long *h_counters = nullptr;

@@ -34,8 +34,9 @@ class Quade(object):
     BATCH_BYTES = int(os.environ.get("QUADE_BATCH_BYTES", 64 << 20))
     #: batches in flight on the device: H2D + kernels of batch N+1 beside the D2H of batch N and the gzip of N-1
     N_SLOTS = 3
-    #: staging buffer sets: one being submitted, one being filled by the reader threads, one spare
-    N_SETS = 3
+    #: a file's page-locked buffer is two halves of HALF_BATCHES x BATCH_BYTES of data behind BATCH_BYTES / 2 of room for
+    #: the rest moved over from the other half (quade_b200/feeder.py): a window can be 2 x BATCH_BYTES long
+    HALF_BATCHES = 1.5
     #: chunks whose files are opened ahead of the one being parsed: a gzip file is inflated by its own thread, so the
     #: files of the next chunks inflate on idle cores while this chunk is on the device (FastqReader.py:30)
     CHUNKS_AHEAD = 3
@@ -117,8 +118,10 @@ class Quade(object):
             print("One of the file is incorrect or unreadable\n" + str(E))
             sys.exit(1)
         self._engine = None
-        self._stage = []
-        self._readpool = None
+        self._stage = []               # two sets of page-locked file buffers (this chunk's, the next chunk's)
+        self._fed = {}                 # chunk -> (readers, feeders) started ahead
+        self._bpr_hint = None          # bytes per record of every file, from the last batch that had pairs
+        self._tickets = []             # per submitted batch of the run: ticket of its bins in the sink (or None)
         import collections
         self._prof = collections.defaultdict(float)
 
@@ -144,6 +147,11 @@ class Quade(object):
 
         print("Start parsing files: {} chunks to be parsed".format(len(self.seq_R1)))
         failure = None
+        self._tickets = []
+        # the main loop shares the interpreter with ~20 reader threads that take the GIL for a moment after every read:
+        # with the default 5 ms switch interval a lock or a thread start in the loop can wait that long
+        switch_interval = sys.getswitchinterval()
+        sys.setswitchinterval(min(switch_interval, 2e-4))
         try:
             # the readers of the first chunks start now: gzip files inflate (libquade_io.so threads) while the CUDA
             # context and the pinned buffers are set up
@@ -153,10 +161,18 @@ class Quade(object):
             self._open_engine()
             Sample.SINK = self._make_sink()
             self._prof["open engine + sink"] += time() - t0
+            t0 = time()
             if self.idx2:
                 self.double_index_parser()
             else:
                 self.simple_index_parser()
+            self._prof["all chunks"] += time() - t0
+            t0 = time()
+            for t in reversed(self._tickets):      # the sink is in order: the last ticket waits for all (and reports errors)
+                if t is not None:
+                    Sample.SINK.wait(t)
+                    break
+            self._prof["wait sink"] += time() - t0
             Sample.FLUSH_ALL()
         except BaseException as E:                  # noqa: B902 -- re-raised below, after the ranks have agreed
             failure = E
@@ -164,6 +180,7 @@ class Quade(object):
             t0 = time()
             self._close_engine()
             self._prof["close"] += time() - t0
+            sys.setswitchinterval(switch_interval)
         if self.world > 1:
             # a rank that failed (blank header, capacity, I/O) must not leave the others waiting in the all-reduce
             others = parallel.any_rank_failed(failure is not None, self.device)
@@ -201,6 +218,13 @@ class Quade(object):
         for i, n in enumerate(mine):
             print("Start parsing chunk {}".format(n + 1))
             self._open_ahead(chunks, mine[i:i + 1 + self.CHUNKS_AHEAD])
+            t0 = time()
+            self._feed(n, chunks[n], i)
+            if i + 1 < len(mine):
+                # the next chunk's first windows fill while this chunk is parsed (its buffers are page-locked once, on
+                # this thread: the library allocates on the calling thread's current device)
+                self._feed(mine[i + 1], chunks[mine[i + 1]], i + 1)
+            self._prof["start feeders"] += time() - t0
             self._parse_chunk(n, chunks[n])
             print("\tEnd of chunk {}".format(n + 1))
 
@@ -210,6 +234,13 @@ class Quade(object):
         for i, n in enumerate(mine):
             print("Start parsing chunk {}/{}".format(n + 1, len(self.seq_R1)))
             self._open_ahead(chunks, mine[i:i + 1 + self.CHUNKS_AHEAD])
+            t0 = time()
+            self._feed(n, chunks[n], i)
+            if i + 1 < len(mine):
+                # the next chunk's first windows fill while this chunk is parsed (its buffers are page-locked once, on
+                # this thread: the library allocates on the calling thread's current device)
+                self._feed(mine[i + 1], chunks[mine[i + 1]], i + 1)
+            self._prof["start feeders"] += time() - t0
             self._parse_chunk(n, chunks[n])
             print("\t{} sequences parsed".format(self._chunk_pairs))     # the reader's line, FastqReader.py:57-58
             print("\tEnd of chunk {}".format(n + 1))
@@ -271,7 +302,13 @@ class Quade(object):
                     self._engine.close()
             finally:
                 self._engine = None
-                for st in getattr(self, "_stage", []):
+                for readers, feeders in self._fed.values():
+                    for f in feeders:
+                        f.close()
+                    for r in readers:
+                        r.close()
+                self._fed = {}
+                for st in self._stage:
                     for b in st:
                         b.free()
                 self._stage = []
@@ -279,57 +316,62 @@ class Quade(object):
                     for r in rs:
                         r.close()
                 self._opened = {}
-                if getattr(self, "_readpool", None) is not None:
-                    self._readpool.shutdown(wait=True)
-                    self._readpool = None
 
-    def _staging(self, ns):
-        """N_SETS sets of page-locked staging buffers, one buffer per file of a chunk (allocated once)."""
-        if len(getattr(self, "_stage", [])) < self.N_SETS or len(self._stage[0]) < ns:
-            for st in getattr(self, "_stage", []):
-                for b in st:
-                    b.free()
-            self._stage = [[self._alloc_staging(2 * self.BATCH_BYTES) for _ in range(ns)] for _ in range(self.N_SETS)]
-        return self._stage
+    def _staging(self, ns, which):
+        """Set `which` (0 / 1: this chunk's, the next chunk's) of page-locked buffers, one per file of a chunk, allocated
+        on first use (two halves each, quade_b200/feeder.py)."""
+        while len(self._stage) <= which:
+            self._stage.append([])
+        st = self._stage[which]
+        while len(st) < ns:
+            st.append(self._alloc_staging(2 * (self.BATCH_BYTES // 2 + int(self.HALF_BATCHES * self.BATCH_BYTES))))
+        return st
+
+    def _feed(self, n, files, i):
+        """Readers and feeder threads of chunk n (the i-th chunk of this rank), started now."""
+        from .feeder import Feeder
+        if n in self._fed:
+            return
+        readers = self._opened.pop(n, None) if hasattr(self, "_opened") else None
+        readers = readers or [FastqReader(f) for f in files]
+        B = self.BATCH_BYTES
+        chunk = max(256, min(16 << 20, B // 2))
+        stage = self._staging(len(files), i % 2)
+        feeders = []
+        self._fed[n] = (readers, feeders)
+        for s in range(len(files)):
+            feeders.append(Feeder(readers[s], stage[s].array, B // 2, chunk))
 
     def _parse_chunk(self, n, files):
         """The body of the reference's `while True` loop for one chunk (Quade.py:210-224 / :240-254), as a pipeline.
 
-        A batch is, per file, the unconsumed tail of the previous batch followed by new bytes.  While batch N is on
-        the device, reader threads fill the next staging set with the new bytes of batch N+1 (placed behind room
-        for the carry-over); as soon as the kernels of batch N are done (quade_peek) its tails are copied in front
-        of them and batch N+1 is submitted; only then batch N is collected -- its D2H copy runs beside the H2D copy
-        and the kernels of N+1 -- and its bins go to the native gzip sink, which compresses and appends them on all
-        host cores while the loop goes on.  The files are read in proportion to their bytes per record, so that
-        every buffer holds about the same number of records.  The chunk ends when a file has run dry (:223, :252).
+        Every file is streamed into its own page-locked buffer by a Feeder thread, ahead of the batches.  A batch is
+        a window of every buffer: the bytes a previous batch left unconsumed and as many more as hold about the same
+        number of records in every file.  While batch N is on the device the feeders keep reading; as soon as its
+        kernels are done (quade_peek) the windows move on and batch N+1 is submitted; only then batch N is collected
+        -- its D2H copy runs beside the H2D copy and the kernels of N+1 -- and its bins go to the native gzip sink,
+        which compresses and appends them on all host cores while the loop goes on.  The chunk ends when a file has
+        run dry (:223, :252).
         """
-        from concurrent.futures import ThreadPoolExecutor
         eng = self._engine
         ns = len(files)
         B = self.BATCH_BYTES
-        head = B                                   # carry-over room in front of the new bytes
+        cap = 2 * B                                # bytes of one file a device slot takes (max_stream_bytes)
         if self.world > 1:
             Sample.FLUSH_ALL()                     # nothing of the previous chunk may land in this chunk's parts
             FastqWriter.PART = n
         if Sample.SINK is not None:
             Sample.SINK.begin_chunk()
-        if getattr(self, "_readpool", None) is None:
-            self._readpool = ThreadPoolExecutor(max_workers=4)
-        sets = [[b.array for b in st] for st in self._staging(ns)]
-        readers = getattr(self, "_opened", {}).pop(n, None) or [FastqReader(f) for f in files]
+        self._feed(n, files, 0)                    # (a caller that did not start them: set 0)
+        readers, feeders = self._fed.pop(n)
         self._chunk_pairs = 0
-        sink_tickets = []                          # per submitted batch: ticket of its bins in the sink (or None)
-        submitted = 0
+        sink_tickets = self._tickets               # batches of the whole run: a slot's arenas outlive the chunk
+        first_ticket = len(sink_tickets)
+        ok = False
         prof = self._prof                          # seconds per pipeline stage (QUADE_PROFILE=1 prints them)
         clock = time
 
-        def fill(k, want):
-            """new bytes of batch k, read by the pool into set k % N_SETS behind the carry-over room"""
-            bufs = sets[k % self.N_SETS]
-            return [self._readpool.submit(readers[s].readinto, bufs[s][head:head + want[s]]) if want[s] and not readers[s].eof
-                    else None for s in range(ns)]
-
-        def finish(res_peek):
+        def finish():
             """collect the oldest batch in flight and hand its bins to the writers"""
             try:
                 res = eng.collect()
@@ -345,41 +387,35 @@ class Quade(object):
             sink_tickets.append(Sample.FINDER(res))
 
         try:
-            want = [min(B, 8 << 20)] * ns          # first batch: a probe that tells the bytes per record of every file
-            futs = fill(0, want)
-            tail = [(0, 0)] * ns                   # (offset, length) of the unconsumed bytes in the previous set
-            bpr = None
+            # first batch of the first chunk: a probe that tells the bytes per record of every file; later chunks
+            # start from the previous chunk's figures
+            bpr = self._bpr_hint if self._bpr_hint is not None and len(self._bpr_hint) == ns else None
+            limit = [min(B, 8 << 20)] * ns if bpr is None else [int(min(cap, B / max(bpr) * bpr[s] + 4096)) for s in range(ns)]
             stalled = 0
+            k = 0
             while True:
-                k = submitted
-                bufs = sets[k % self.N_SETS]
                 t0 = clock()
-                got = [f.result() if f is not None else 0 for f in futs]
-                prof["wait readers"] += clock() - t0
-                eof = [r.eof for r in readers]
-                t0 = clock()
-                views = []
                 for s in range(ns):
-                    off, ln = tail[s]
-                    if ln:
-                        bufs[s][head - ln:head] = sets[(k - 1) % self.N_SETS][s][off:off + ln]
-                    views.append(bufs[s][head - ln:head + got[s]])
-                prof["carry-over copy"] += clock() - t0
+                    feeders[s].wait_for(limit[s])
+                wins = [feeders[s].window(limit[s]) for s in range(ns)]
+                prof["wait readers"] += clock() - t0
+                views = [w[0] for w in wins]
+                eof = [w[1] for w in wins]
                 t0 = clock()
-                if k >= self.N_SLOTS and sink_tickets[k - self.N_SLOTS] is not None:
-                    Sample.SINK.wait(sink_tickets[k - self.N_SLOTS])   # the slot's output arenas are about to be reused
+                K = first_ticket + k                # batches submitted since the start of the run
+                if K >= self.N_SLOTS and sink_tickets[K - self.N_SLOTS] is not None:
+                    Sample.SINK.wait(sink_tickets[K - self.N_SLOTS])   # the slot's output arenas are about to be reused
                 prof["wait sink"] += clock() - t0
                 t0 = clock()
                 eng.submit(views, last=eof, ticket=k)
-                submitted += 1
                 prof["submit"] += clock() - t0
                 t0 = clock()
                 if k >= 1:
-                    finish(None)                   # batch k-1: D2H beside the H2D and the kernels of batch k
+                    finish()                       # batch k-1: D2H beside the H2D and the kernels of batch k
                 prof["collect + sink append"] += clock() - t0
                 t0 = clock()
                 try:
-                    res = eng.peek()               # kernels of batch k done: carry-over known
+                    res = eng.peek()               # kernels of batch k done (so is its H2D copy): the windows may move
                 except RuntimeError as E:
                     if getattr(E, "code", None) == -1:
                         eng.collect_discard()
@@ -387,46 +423,49 @@ class Quade(object):
                     raise
                 prof["peek"] += clock() - t0
                 prof["batches"] += 1
+                k += 1
                 self._chunk_pairs += res.n_pairs
-                done = res.chunk_end
-                new_tail = []
+                t0 = clock()
                 for s in range(ns):
-                    c = int(res.consumed[s])
-                    new_tail.append((head - tail[s][1] + c, len(views[s]) - c))
-                if not done:
-                    # bytes per record of every file -> new bytes so that all buffers hold about the same number of
-                    # records; a file that is ahead of the others reads less
-                    if res.n_pairs:
-                        bpr = [max(1.0, int(res.consumed[s]) / res.n_pairs) for s in range(ns)]
-                    progressed = res.n_pairs > 0 or any(int(c) > 0 for c in res.consumed[:ns]) or any(got)
-                    stalled = 0 if progressed else stalled + 1
-                    if bpr is None:
-                        want = [min(B, max(w, 1 << 20) * 2) for w in want]     # no complete pair yet: read more
-                    else:
-                        pairs = B / max(bpr)
-                        want = [int(min(B, max(0.0, pairs * bpr[s] - new_tail[s][1]))) & ~15 for s in range(ns)]
-                        if stalled:
-                            want = [min(B, max(w, 1 << 20) * (2 ** stalled)) for w in want]
-                    # a file that is ahead of the others keeps its tail and reads nothing: tail + new bytes must fit the
-                    # carry-over room of the next batch whatever that batch consumes
-                    want = [max(0, min(w, 2 * B - head, head - new_tail[s][1])) for s, w in enumerate(want)]
-                    if stalled > 8 or any(t[1] > head for t in new_tail):
+                    feeders[s].consume(int(res.consumed[s]))
+                prof["move windows"] += clock() - t0
+                if res.chunk_end:
+                    finish()
+                    ok = True
+                    break
+                # bytes per record of every file -> windows that hold about the same number of records; a file that is
+                # ahead of the others keeps its surplus in its buffer
+                if res.n_pairs:
+                    bpr = [max(1.0, int(res.consumed[s]) / res.n_pairs) for s in range(ns)]
+                    self._bpr_hint = bpr
+                progressed = res.n_pairs > 0 or any(int(c) > 0 for c in res.consumed[:ns])
+                stalled = 0 if progressed else stalled + 1
+                if bpr is None or stalled:
+                    # no complete pair in the windows: longer ones (the end of a feeder's half also lands here, once)
+                    if stalled > 8:
                         raise IOError("a FASTQ record of chunk {} is larger than the staging buffer "
                                       "(QUADE_BATCH_BYTES={})".format(n + 1, B))
-                    futs = fill(k + 1, want)
-                tail = new_tail
-                if done:
-                    finish(res)
-                    break
+                    limit = [min(cap, max(w, 1 << 10) * 2) for w in limit]
+                else:
+                    pairs = B / max(bpr)
+                    limit = [int(min(cap, pairs * bpr[s] + 4096)) for s in range(ns)]
         finally:
+            t0 = clock()
+            for f in feeders:
+                f.close()
+            prof["stop feeders"] += clock() - t0
             while eng.in_flight:                   # an exception above: leave no batch in flight
                 try:
                     eng.collect()
                 except Exception:
                     pass
-            for t in sink_tickets:
-                if t is not None and Sample.SINK is not None:
-                    Sample.SINK.wait(t)
+            if not ok:                             # an exception above: the sink may not outlive the arenas either
+                for t in sink_tickets[first_ticket:]:
+                    if t is not None and Sample.SINK is not None:
+                        try:
+                            Sample.SINK.wait(t)
+                        except Exception:
+                            pass
             for r in readers:
                 r.close()
 

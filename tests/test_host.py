@@ -327,3 +327,51 @@ def test_native_gzip_reader_reports_damage_after_the_good_bytes(tmp_path, monkey
     r.close()
     with pytest.raises(IOError):
         FastqReader(str(tmp_path / "missing.gz"))
+
+
+def test_feeder_windows_reassemble_the_file(tmp_path):
+    """quade_b200/feeder.py: whatever the window limits and the bytes a batch consumes, the consumed bytes are the
+    file, in order, through any number of wraps of the buffer."""
+    from quade_b200.feeder import Feeder
+    from quade_b200.pyfastq import FastqReader
+    rng = np.random.default_rng(11)
+    data = bytes(rng.integers(0, 256, 200_000, dtype=np.uint8))
+    p = tmp_path / "blob.fastq"
+    p.write_bytes(data)
+    for head, ring, chunk in ((1024, 3, 512), (4096, 3, 2048), (64, 2, 37), (1 << 16, 3, 1 << 15)):
+        buf = np.zeros(2 * head * (1 + ring), dtype=np.uint8)          # two halves of head + ring * head bytes
+        f = Feeder(FastqReader(str(p)), buf, head, chunk)
+        out = bytearray()
+        stuck = 0
+        while True:
+            limit = int(rng.integers(1, 2 * head + 1))
+            f.wait_for(limit)
+            view, last = f.window(limit)
+            assert len(view) <= limit
+            take = int(rng.integers(0, len(view) + 1)) if len(view) else 0
+            if rng.random() < 0.3:
+                take = len(view)
+            out += view[:take].tobytes()
+            rest = f.consume(take)
+            if last and take == len(view):
+                assert rest == 0
+                break
+            stuck = stuck + 1 if take == 0 else 0
+            assert stuck < 200
+        f.close()
+        assert bytes(out) == data, (head, ring, chunk)
+
+
+def test_feeder_surfaces_reader_errors(tmp_path):
+    from quade_b200.feeder import Feeder
+
+    class Broken:
+        eof = False
+
+        def readinto(self, arr):
+            raise IOError("disk gone")
+
+    f = Feeder(Broken(), np.zeros(8192, dtype=np.uint8), 1024, 512)
+    with pytest.raises(IOError):
+        f.wait_for(100)
+    f.close()
