@@ -1,6 +1,10 @@
 // quade_bins.cuh -- k_binscan_* and k_offsets (included by quade_kernels.cu)
 #pragma once
 
+#ifndef QUADE_OFFSETS_BALLOT
+#define QUADE_OFFSETS_BALLOT 1      /* peer groups from ballots over the bin's bits instead of MATCH.ANY (0.039 -> 0.033 ms) */
+#endif
+
 namespace quade {
 namespace {
 
@@ -110,18 +114,43 @@ __global__ void __launch_bounds__(256) k_offsets(const __grid_constant__ BatchDe
         run2[i] = (uint32_t)b.bin_off[nb + 1 + i] + hg[nb + i];
     }
     __syncthreads();
+    const uint32_t bin_bits = 32u - (uint32_t)__clz(max(nb, 2) - 1);
     const uint32_t n_pairs = S->n_pairs, p0 = blockIdx.x * b.pairs_per_block;
     uint32_t end = p0 + b.pairs_per_block;
     if (end > n_pairs) end = n_pairs;
+    // the inputs of the next 256 pairs are loaded while these are ranked: a round trip to L2 per chunk was a third of
+    // the kernel's time
+    uint32_t n_bin = 0xffffffffu, n_l1 = 0u, n_l2 = 0u;
+    if (p0 + tid < end) {
+        n_bin = b.cls[p0 + tid] & 0xffffu;
+        n_l1 = b.len1[p0 + tid];
+        n_l2 = b.len2[p0 + tid];
+    }
     for (uint32_t c0 = p0; c0 < end; c0 += 256) {
         const uint32_t p = c0 + tid;
         const bool active = p < end;
-        const uint32_t bin = active ? (b.cls[p] & 0xffffu) : 0xffffffffu;
-        const uint32_t l1 = active ? b.len1[p] : 0u, l2 = active ? b.len2[p] : 0u;
+        const uint32_t bin = n_bin, l1 = n_l1, l2 = n_l2;
+        n_bin = 0xffffffffu;
+        n_l1 = n_l2 = 0u;
+        if (p + 256u < end) {
+            n_bin = b.cls[p + 256u] & 0xffffu;
+            n_l1 = b.len1[p + 256u];
+            n_l2 = b.len2[p + 256u];
+        }
         // stable rank inside the warp: output bytes of the lower lanes that go to the same bin.  match.any gives
         // the lanes sharing this lane's bin; groups are small (hundreds of bins), so the loop runs 1-3 times
         // instead of the 32 x 3 shuffles of an all-pairs comparison
+#if QUADE_OFFSETS_BALLOT
+        // lanes with this lane's bin, from one ballot per bit of the bin index (MATCH.ANY costs ~110 cycles of the ADU pipe)
+        unsigned peers = __ballot_sync(0xffffffffu, active);
+        if (!active) peers = ~peers;
+        for (uint32_t bit = 0; bit < bin_bits; ++bit) {
+            const unsigned m = __ballot_sync(0xffffffffu, (bin >> bit) & 1u);
+            peers &= (bin >> bit) & 1u ? m : ~m;
+        }
+#else
         const unsigned peers = __match_any_sync(0xffffffffu, bin);
+#endif
         const bool later = (peers >> lane) > 1u;                // a higher lane writes to the same bin
         unsigned rem = peers & ((1u << lane) - 1u);
         uint32_t pre1 = 0, pre2 = 0;
