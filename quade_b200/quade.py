@@ -29,8 +29,8 @@ class Quade(object):
     VERSION = "Quade 0.3.2"
     USAGE = "Usage: %prog -c Conf.txt [-i -h]"
 
-    #: new bytes of the largest file staged per batch (the other files in proportion to their record size);
-    #: env QUADE_BATCH_BYTES.  Staging buffers and device slots are sized for twice that (carry-over room).
+    #: bytes of the largest file in a batch (the other files in proportion to their record size); env
+    #: QUADE_BATCH_BYTES.  A device slot takes twice that per file: windows grow when no complete pair fits.
     BATCH_BYTES = int(os.environ.get("QUADE_BATCH_BYTES", 64 << 20))
     #: batches in flight on the device: H2D + kernels of batch N+1 beside the D2H of batch N and the gzip of N-1
     N_SLOTS = 3
@@ -253,7 +253,7 @@ class Quade(object):
 
     def _open_engine(self):
         """The C-ABI context of this process's GPU (loads libquade_b200.so; raises without a CUDA device: there is
-        no CPU path).  Slots and staging buffers are sized for 2 x BATCH_BYTES: carry-over plus new bytes."""
+        no CPU path).  A slot takes 2 x BATCH_BYTES of every file (the longest window _parse_chunk submits)."""
         if self._engine is None:
             from .demux import DemuxContext
             self._engine = DemuxContext(self.idx2, self.spans(), self.minimal_qual,
