@@ -92,11 +92,16 @@ class Feeder:
                     return end - self.rd
                 self._cv.wait()
 
-    def window(self, limit):
-        """(view of the next batch's bytes of this file, True if they end the file)"""
+    def window(self, limit, cap=0):
+        """(view of the next batch's bytes of this file, True if they end the file).  `limit` bytes at most -- but what is
+        left of a half the thread has moved on from goes in ONE window if that is not much more (a third, and no more
+        than `cap`): a window that stops just short of the end of the half would leave megabytes to move over, or a
+        tiny batch, instead of a partial record."""
         with self._cv:
             end, _ = self._end()
             n = min(end - self.rd, int(limit))
+            if self.w_half != self.r_half and end - self.rd <= min(int(cap), int(limit) + int(limit) // 3):
+                n = end - self.rd
             last = self.eof and self.w_half == self.r_half and n == end - self.rd
             return self.buf[self.rd:self.rd + n], last
 

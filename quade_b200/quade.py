@@ -30,13 +30,15 @@ class Quade(object):
     USAGE = "Usage: %prog -c Conf.txt [-i -h]"
 
     #: bytes of the largest file in a batch (the other files in proportion to their record size); env
-    #: QUADE_BATCH_BYTES.  A device slot takes twice that per file: windows grow when no complete pair fits.
+    #: QUADE_BATCH_BYTES.  A device slot takes SLOT_BATCHES times that per file: windows grow when no complete pair fits.
     BATCH_BYTES = int(os.environ.get("QUADE_BATCH_BYTES", 64 << 20))
+    SLOT_BATCHES = 1.25
     #: batches in flight on the device: H2D + kernels of batch N+1 beside the D2H of batch N and the gzip of N-1
     N_SLOTS = 3
     #: a file's page-locked buffer is two halves of HALF_BATCHES x BATCH_BYTES of data behind BATCH_BYTES / 2 of room for
-    #: the rest moved over from the other half (quade_b200/feeder.py): a window can be 2 x BATCH_BYTES long
-    HALF_BATCHES = 1.5
+    #: the rest moved over from the other half (quade_b200/feeder.py).  One batch per half: the window of the largest
+    #: file is the whole half, so that what moves over is a partial record
+    HALF_BATCHES = 1.0
     #: chunks whose files are opened ahead of the one being parsed: a gzip file is inflated by its own thread, so the
     #: files of the next chunks inflate on idle cores while this chunk is on the device (FastqReader.py:30)
     CHUNKS_AHEAD = 3
@@ -251,16 +253,19 @@ class Quade(object):
         """python slices of idx1, idx2, mol1, mol2 in the order of the C-ABI (QUADE_SPAN_*)"""
         return [(p["start"], p["end"]) for p in (self.idx1_pos, self.idx2_pos, self.mol1_pos, self.mol2_pos)]
 
+    def _slot_bytes(self):
+        return (int(self.SLOT_BATCHES * self.BATCH_BYTES) + 15) & ~15
+
     def _open_engine(self):
         """The C-ABI context of this process's GPU (loads libquade_b200.so; raises without a CUDA device: there is
-        no CPU path).  A slot takes 2 x BATCH_BYTES of every file (the longest window _parse_chunk submits)."""
+        no CPU path).  A slot takes SLOT_BATCHES x BATCH_BYTES of every file (the longest window _parse_chunk submits)."""
         if self._engine is None:
             from .demux import DemuxContext
             self._engine = DemuxContext(self.idx2, self.spans(), self.minimal_qual,
                                         [s.index for s in Sample.SAMPLE_LIST],
                                         write_undetermined=Sample.WRITE_UNDETERMINED, write_pass=Sample.WRITE_PASS,
                                         write_fail=Sample.WRITE_FAIL, device=self.device,
-                                        max_stream_bytes=2 * self.BATCH_BYTES, n_slots=self.N_SLOTS)
+                                        max_stream_bytes=self._slot_bytes(), n_slots=self.N_SLOTS)
         return self._engine
 
     def _chunk_plan(self):
@@ -309,7 +314,7 @@ class Quade(object):
                         r.close()
                 self._fed = {}
                 for st in self._stage:
-                    for b in st:
+                    for b, _ in st:
                         b.free()
                 self._stage = []
                 for rs in getattr(self, "_opened", {}).values():
@@ -317,14 +322,26 @@ class Quade(object):
                         r.close()
                 self._opened = {}
 
-    def _staging(self, ns, which):
+    def _staging(self, files, which):
         """Set `which` (0 / 1: this chunk's, the next chunk's) of page-locked buffers, one per file of a chunk, allocated
-        on first use (two halves each, quade_b200/feeder.py)."""
+        on first use (two halves each, quade_b200/feeder.py).  Returns [(buffer, head bytes)].  A file much smaller than
+        the largest of its chunk (an index file beside the insert files) holds as many records in a quarter or half
+        of the bytes, and page-locking memory costs ~0.4 s per GiB at start-up."""
         while len(self._stage) <= which:
             self._stage.append([])
         st = self._stage[which]
-        while len(st) < ns:
-            st.append(self._alloc_staging(2 * (self.BATCH_BYTES // 2 + int(self.HALF_BATCHES * self.BATCH_BYTES))))
+        sizes = []
+        for f in files:
+            try:
+                sizes.append(os.path.getsize(f))
+            except OSError:
+                sizes.append(0)
+        top = max(sizes + [1])
+        while len(st) < len(files):
+            share = sizes[len(st)] / top
+            scale = 0.25 if share <= 0.2 else (0.5 if share <= 0.4 else 1.0)
+            b = max(512, int(scale * self.BATCH_BYTES)) & ~15
+            st.append((self._alloc_staging(2 * (b // 2 + int(self.HALF_BATCHES * b))), b // 2))
         return st
 
     def _feed(self, n, files, i):
@@ -336,11 +353,12 @@ class Quade(object):
         readers = readers or [FastqReader(f) for f in files]
         B = self.BATCH_BYTES
         chunk = max(256, min(16 << 20, B // 2))
-        stage = self._staging(len(files), i % 2)
+        stage = self._staging(files, i % 2)
         feeders = []
         self._fed[n] = (readers, feeders)
         for s in range(len(files)):
-            feeders.append(Feeder(readers[s], stage[s].array, B // 2, chunk))
+            buf, head = stage[s]
+            feeders.append(Feeder(readers[s], buf.array, head, min(chunk, max(256, head))))
 
     def _parse_chunk(self, n, files):
         """The body of the reference's `while True` loop for one chunk (Quade.py:210-224 / :240-254), as a pipeline.
@@ -356,7 +374,7 @@ class Quade(object):
         eng = self._engine
         ns = len(files)
         B = self.BATCH_BYTES
-        cap = 2 * B                                # bytes of one file a device slot takes (max_stream_bytes)
+        cap = self._slot_bytes()                   # bytes of one file a device slot takes (max_stream_bytes)
         if self.world > 1:
             Sample.FLUSH_ALL()                     # nothing of the previous chunk may land in this chunk's parts
             FastqWriter.PART = n
@@ -397,7 +415,7 @@ class Quade(object):
                 t0 = clock()
                 for s in range(ns):
                     feeders[s].wait_for(limit[s])
-                wins = [feeders[s].window(limit[s]) for s in range(ns)]
+                wins = [feeders[s].window(limit[s], cap) for s in range(ns)]
                 prof["wait readers"] += clock() - t0
                 views = [w[0] for w in wins]
                 eof = [w[1] for w in wins]

@@ -345,9 +345,10 @@ def test_feeder_windows_reassemble_the_file(tmp_path):
         stuck = 0
         while True:
             limit = int(rng.integers(1, 2 * head + 1))
+            cap = int(rng.integers(0, 3 * head))
             f.wait_for(limit)
-            view, last = f.window(limit)
-            assert len(view) <= limit
+            view, last = f.window(limit, cap)
+            assert len(view) <= max(limit, cap)
             take = int(rng.integers(0, len(view) + 1)) if len(view) else 0
             if rng.random() < 0.3:
                 take = len(view)
